@@ -1,0 +1,4 @@
+#define CV_CPU_SIMD_FILENAME "convert_scale.simd.hpp"
+#define CV_CPU_DISPATCH_MODES_ALL BASELINE
+
+#undef CV_CPU_SIMD_FILENAME
