@@ -7,6 +7,9 @@
 #ifndef OPENCV_CVCONFIG_H_INCLUDED
 #define OPENCV_CVCONFIG_H_INCLUDED
 #define BUILD_SHARED_LIBS
+/* the reference's default: CV_ENABLE_INTRINSICS=ON (CMakeLists.txt:501) -> its SSE2 code paths */
+#define CV_ENABLE_INTRINSICS
+#define HAVE_INTTYPES_H 1
 #define HAVE_PTHREAD
 #define HAVE_MEMALIGN 1
 #define HAVE_POSIX_MEMALIGN 1
