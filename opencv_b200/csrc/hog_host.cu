@@ -1,0 +1,1002 @@
+// hog_host.cu -- host side of the B200-native HOG detector: the C ABI of include/hogb200.h.
+//
+// Mirrors HOG_Impl (modules/cudaobjdetect/src/hog.cpp:139-689): same parameters, defaults, argument checks and
+// call sequence, but
+//   * the whole pyramid of a frame is three launches (resize, fused gradient+histogram, SVM+compaction) instead
+//     of ~5 launches + 11 constant copies + 2 device syncs + 1 blocking download PER LEVEL (hog.cpp:449-482);
+//   * all scratch lives in a per-handle workspace sized once per frame shape (no BufferPool traffic);
+//   * hits come back as one compact candidate list per frame (or per chunk of frames), sorted on the host into
+//     the reference's (level, row-major) order before rect scaling and groupRectangles.
+// No CPU fallback: every work call needs the CUDA device the handle was created on.
+#include "../../include/hogb200.h"
+#include "hog_internal.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cfloat>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace hogk;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) {                                                                  \
+            cudaGetLastError();                                                                    \
+            return fail(HOGB200_CUDA_ERROR, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+        }                                                                                          \
+    } while (0)
+
+inline int cvRound(double v) { return (int)lrint(v); }          // round-half-even, as the reference's cvRound
+inline int cvFloorF(float v) { int i = (int)v; return i - (v < (float)i); }
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 8 + 64;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+template <typename T>
+struct PinBuf {
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 8 + 64;
+        cudaError_t e = cudaMallocHost((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct LevelHost {
+    double scale; int w, h; int nbx, nby; int nwx, nwy;
+    long long hist_off, score_off; size_t img_off; int pitch; int mode;
+};
+
+// Everything that depends only on (frame shape, channels, parameters): level table, resize coefficient
+// tables, kernel work lists.  Built once, reused for every frame of that shape.
+struct Plan {
+    int W = 0, H = 0, cn = 0;
+    int nlevels_param = 0; double scale0 = 0; int win_w = 0, win_h = 0, sx = 0, sy = 0;
+    bool single_level = false;
+    std::vector<LevelHost> lv;
+    long long hist_floats = 0, score_floats = 0, pyr_pixels = 0, nblocks = 0, nwindows = 0;
+    size_t pyr_bytes = 0;
+    int n_resize = 0, n_hist = 0, n_svm = 0;
+    DevBuf<LevelDesc> d_levels; DevBuf<ResizeCoef> d_xtab, d_ytab;
+    DevBuf<ResizeItem> d_ritems; DevBuf<HistItem> d_hitems; DevBuf<SvmItem> d_sitems;
+    const uint8_t* pyr_base = nullptr;   // pyramid buffer the level pointers were built for
+    bool valid = false;
+};
+
+}  // namespace
+
+struct hogb200 {
+    int device = 0;
+    hogb200_geom g;
+    // parameters (defaults hog.cpp:241-249)
+    double win_sigma = -1.0, l2hys = 0.2; int gamma = 1; int nlevels = 64; double hit_threshold = 0.0;
+    int win_stride_x = 8, win_stride_y = 8; double scale0 = 1.05; int group_threshold = 2;
+    int descr_format = HOGB200_DESCR_FORMAT_COL_BY_COL;
+    // detectors: reordered to row-major blocks (hog.cpp:303-317) on the device, bias on the host
+    DevBuf<float> d_det[kMaxDet]; float bias[kMaxDet] = {0, 0, 0, 0}; bool have_det[kMaxDet] = {false, false, false, false};
+    // streams
+    cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
+    // workspace
+    DevBuf<uint8_t> d_frame[2]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
+    DevBuf<unsigned char> d_cand;   // [16-byte header: counter][Candidate * cap]
+    size_t cand_cap = 0;
+    PinBuf<unsigned char> h_cand;
+    DevBuf<float> d_desc;
+    Plan plan, plan1;               // multi-scale plan and single-scale plan
+    // timing
+    int timing = 0; cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    hogb200_timings last = {};
+};
+
+namespace {
+
+int win_bx(const hogb200* h) { return (h->g.win_w - kBlock) / kCell + 1; }
+int win_by(const hogb200* h) { return (h->g.win_h - kBlock) / kCell + 1; }
+
+int use_device(const hogb200* h)
+{
+    CK(cudaSetDevice(h->device));
+    return HOGB200_OK;
+}
+
+// Separable block window (HOGCache::init, objdetect/src/hog.cpp:653-728 Gaussian, :763-835 cell interpolation):
+// weight(i,j) = gauss(i)gauss(j) * wcell_cy(i) * wcell_cx(j); a0/a1 = the 1-D factor for cell 0 / cell 1.
+BlockWeights make_weights(double win_sigma)
+{
+    BlockWeights W;
+    const float sigma = (float)(win_sigma >= 0 ? win_sigma : (kBlock + kBlock) / 8.0);   // hog.cpp:288-291
+    const float scale = 1.f / (sigma * sigma * 2);
+    for (int i = 0; i < 16; i++) {
+        float d = i - kBlock * 0.5f;
+        const float gss = std::exp(-(d * d) * scale);
+        float cell = (i + 0.5f) / kCell - 0.5f;
+        const int c0 = cvFloorF(cell);
+        cell -= c0;
+        float w0 = 0.f, w1 = 0.f;                  // contributions to cell 0 and cell 1; cells -1 and 2 are dropped
+        if (c0 == 0) w0 = 1.f - cell; else if (c0 + 1 == 0) w0 = cell;
+        if (c0 == 1) w1 = 1.f - cell; else if (c0 + 1 == 1) w1 = cell;
+        W.a0[i] = gss * w0;
+        W.a1[i] = gss * w1;
+    }
+    return W;
+}
+
+}  // namespace
+
+namespace {
+
+// ---- level enumeration: HOG_Impl::detectMultiScale, cudaobjdetect/src/hog.cpp:424-441,453 -----------------
+void enumerate_levels(int W, int H, int win_w, int win_h, double scale0, int nlevels, std::vector<double>& scales)
+{
+    scales.clear();
+    double scale = 1.0;
+    int levels = 0;
+    for (levels = 0; levels < nlevels; levels++) {
+        scales.push_back(scale);
+        if (cvRound(W / scale) < win_w || cvRound(H / scale) < win_h || scale0 <= 1) break;
+        scale *= scale0;
+    }
+    levels = std::max(levels, 1);
+    scales.resize(levels);
+}
+
+// ---- cv::resize INTER_LINEAR coefficient tables, imgproc/src/resize.cpp:3609-3696 (double -> float -> Q11)
+void resize_table(int src, int dst, bool is_x, std::vector<ResizeCoef>& out)
+{
+    const double inv_scale = (double)dst / src;     // resize.cpp:3730-3731
+    const double scale = 1. / inv_scale;            // :3481
+    for (int d = 0; d < dst; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = cvFloorF(f);
+        f -= s;
+        if (is_x) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= src - 1) { f = 0; s = src - 1; }   // :3631-3636 (xmax handling: second tap has weight 0)
+        }
+        ResizeCoef c;
+        c.ofs = s;
+        c.c0 = (short)lrintf((1.f - f) * 2048);
+        c.c1 = (short)lrintf(f * 2048);
+        out.push_back(c);
+    }
+}
+
+bool is_exact_half(int src_w, int src_h, int dst_w, int dst_h)
+{
+    // resize.cpp:3481-3489,3523-3524: scale == 2 in both directions (tested on the doubles the reference forms)
+    const double sx = 1. / ((double)dst_w / src_w), sy = 1. / ((double)dst_h / src_h);
+    return std::abs(sx - 2) < DBL_EPSILON && std::abs(sy - 2) < DBL_EPSILON && lrint(sx) == 2 && lrint(sy) == 2;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
+{
+    if (P.valid && P.W == W && P.H == H && P.cn == cn && P.single_level == single &&
+        P.nlevels_param == h->nlevels && P.scale0 == h->scale0 && P.win_w == h->g.win_w && P.win_h == h->g.win_h &&
+        P.sx == h->win_stride_x && P.sy == h->win_stride_y && P.pyr_base == h->d_pyr.p)
+        return HOGB200_OK;
+    P.valid = false;
+    P.W = W; P.H = H; P.cn = cn; P.single_level = single;
+    P.nlevels_param = h->nlevels; P.scale0 = h->scale0; P.win_w = h->g.win_w; P.win_h = h->g.win_h;
+    P.sx = h->win_stride_x; P.sy = h->win_stride_y;
+
+    std::vector<double> scales;
+    if (single) scales.assign(1, 1.0);
+    else enumerate_levels(W, H, h->g.win_w, h->g.win_h, h->scale0, h->nlevels, scales);
+    if ((int)scales.size() > kMaxLevels) return fail(HOGB200_BAD_ARG, "too many pyramid levels (max 256)");
+
+    const int wbx = win_bx(h), wby = win_by(h);
+    const int sbx = h->win_stride_x / kCell, sby = h->win_stride_y / kCell;
+    P.lv.clear();
+    P.hist_floats = P.score_floats = P.pyr_pixels = P.nblocks = P.nwindows = 0;
+    size_t pyr = 0;
+    std::vector<ResizeCoef> xtab, ytab;
+    std::vector<ResizeItem> ritems; std::vector<HistItem> hitems; std::vector<SvmItem> sitems;
+    std::vector<LevelDesc> descs;
+    for (size_t i = 0; i < scales.size(); i++) {
+        LevelHost L;
+        L.scale = scales[i];
+        L.w = cvRound(W / L.scale); L.h = cvRound(H / L.scale);                 // hog.cpp:453
+        L.nbx = L.w >= kBlock ? (L.w - kBlock) / kCell + 1 : 0;
+        L.nby = L.h >= kBlock ? (L.h - kBlock) / kCell + 1 : 0;
+        if (L.nbx <= 0 || L.nby <= 0) L.nbx = L.nby = 0;
+        // numPartsWithin, hog.cpp:267-276; an image smaller than the window has no windows
+        L.nwx = L.w >= h->g.win_w ? (L.w - h->g.win_w + h->win_stride_x) / h->win_stride_x : 0;
+        L.nwy = L.h >= h->g.win_h ? (L.h - h->g.win_h + h->win_stride_y) / h->win_stride_y : 0;
+        if (L.nwx <= 0 || L.nwy <= 0) L.nwx = L.nwy = 0;
+        L.hist_off = P.hist_floats; P.hist_floats += (long long)L.nbx * L.nby * kHist;
+        L.score_off = P.score_floats; P.score_floats += (long long)L.nwx * L.nwy;
+        P.pyr_pixels += (long long)L.w * L.h; P.nblocks += (long long)L.nbx * L.nby; P.nwindows += (long long)L.nwx * L.nwy;
+        LevelDesc D; memset(&D, 0, sizeof D);
+        if (L.w == W && L.h == H) {                 // hog.cpp:456-459: the frame itself
+            L.mode = 0; L.img_off = 0; L.pitch = 0;
+            D.img = nullptr; D.pitch = 0;
+        } else {
+            L.mode = is_exact_half(W, H, L.w, L.h) ? 2 : 1;
+            L.pitch = (int)align_up((size_t)L.w * cn, 64);
+            L.img_off = pyr; pyr += align_up((size_t)L.pitch * L.h, 256);
+            D.xtab_off = (int)xtab.size(); D.ytab_off = (int)ytab.size();
+            if (L.mode == 1) { resize_table(W, L.w, true, xtab); resize_table(H, L.h, false, ytab); }
+            const int tw = cn == 4 ? 32 : 128;
+            for (int y = 0; y < L.h; y += 8)
+                for (int x = 0; x < L.w; x += tw) ritems.push_back(ResizeItem{(short)i, (short)x, (short)y, 0});
+        }
+        D.w = L.w; D.h = L.h; D.nbx = L.nbx; D.nby = L.nby; D.nwx = L.nwx; D.nwy = L.nwy;
+        D.hist_off = L.hist_off; D.score_off = L.score_off; D.mode = L.mode; D.pitch = L.pitch;
+        const int tbx = hist_tile_blocks_x(), sby_ = hist_strip_blocks_y();
+        for (int by = 0; by < L.nby; by += sby_)
+            for (int bx = 0; bx < L.nbx; bx += tbx)
+                hitems.push_back(HistItem{(short)i, (short)bx, (short)by, (short)std::min(sby_, L.nby - by)});
+        const int vwx = L.nbx - wbx + 1, vwy = L.nby - wby + 1;
+        if (L.nwx > 0 && vwx > 0 && vwy > 0)
+            for (int wy = 0; wy < vwy; wy += svm_tile_wy())
+                for (int wx = 0; wx < vwx; wx += svm_tile_wx()) sitems.push_back(SvmItem{(short)i, (short)wx, (short)wy, 0});
+        P.lv.push_back(L); descs.push_back(D);
+    }
+    (void)sbx; (void)sby;
+    P.pyr_bytes = pyr;
+    CK(h->d_pyr.reserve(pyr + 256));
+    for (size_t i = 0; i < descs.size(); i++)
+        if (P.lv[i].mode != 0) descs[i].img = h->d_pyr.p + P.lv[i].img_off;
+    P.pyr_base = h->d_pyr.p;
+    CK(h->d_hist.reserve((size_t)P.hist_floats + 64));
+    P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size();
+    cudaStream_t st = h->stream;
+    CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use
+    auto up = [&](auto& buf, const auto& v) -> cudaError_t {
+        cudaError_t e = buf.reserve(v.size() + 1);
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpy(buf.p, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
+    };
+    CK(up(P.d_levels, descs)); CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
+    CK(up(P.d_ritems, ritems)); CK(up(P.d_hitems, hitems)); CK(up(P.d_sitems, sitems));
+    P.valid = true;
+    return HOGB200_OK;
+}
+
+}  // namespace
+
+namespace {
+
+struct FrameRef { const uint8_t* dev; int pitch; };
+
+int check_image(const hogb200_image* img)
+{
+    if (!img || !img->data) return fail(HOGB200_BAD_ARG, "image is null");
+    if (img->channels != 1 && img->channels != 4)
+        return fail(HOGB200_BAD_ARG, "image type must be CV_8UC1 or CV_8UC4 (cudaobjdetect/src/hog.cpp:340)");
+    if (img->width <= 0 || img->height <= 0 || img->pitch < (size_t)img->width * img->channels)
+        return fail(HOGB200_BAD_ARG, "bad image size / pitch");
+    if (img->width > 32000 || img->height > 32000) return fail(HOGB200_BAD_ARG, "image too large");
+    return HOGB200_OK;
+}
+
+// Make the frame device-resident and 4-byte addressable.  buf = 0/1 selects the staging buffer (double
+// buffering in the batch path).  Copies are issued on `st`.
+int stage_frame(hogb200* h, const hogb200_image* img, int buf, cudaStream_t st, FrameRef& out)
+{
+    const int cn = img->channels;
+    const size_t row = (size_t)img->width * cn;
+    if (img->on_device && ((uintptr_t)img->data % 4 == 0) && (img->pitch % 4 == 0 || cn == 1) && img->pitch < (1u << 30)) {
+        out.dev = (const uint8_t*)img->data; out.pitch = (int)img->pitch;
+        return HOGB200_OK;
+    }
+    const size_t pitch = align_up(row, 64);
+    CK(h->d_frame[buf].reserve(pitch * img->height + 64));
+    CK(cudaMemcpy2DAsync(h->d_frame[buf].p, pitch, img->data, img->pitch, row, img->height,
+                         img->on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    out.dev = h->d_frame[buf].p; out.pitch = (int)pitch;
+    return HOGB200_OK;
+}
+
+int ensure_cand(hogb200* h, size_t cap)
+{
+    if (cap < 4096) cap = 4096;
+    if (cap > h->cand_cap || !h->d_cand.p) {
+        CK(cudaStreamSynchronize(h->stream));
+        CK(h->d_cand.reserve(16 + cap * sizeof(Candidate)));
+        h->cand_cap = (h->d_cand.cap - 16) / sizeof(Candidate);
+    }
+    return HOGB200_OK;
+}
+
+// Queue the three kernels of one frame on the handle's stream.
+int queue_frame(hogb200* h, Plan& P, FrameRef f, int ndet, const int* slots, float thresh, float* d_scores,
+                int tag, int* launches)
+{
+    cudaStream_t st = h->stream;
+    if (h->timing) cudaEventRecord(h->ev[1], st);
+    if (P.n_resize) {
+        launch_resize(f.dev, f.pitch, P.W, P.H, P.cn, P.d_levels.p, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
+        (*launches)++;
+    }
+    if (h->timing) cudaEventRecord(h->ev[2], st);
+    if (P.n_hist) {
+        launch_hist(f.dev, f.pitch, P.d_levels.p, P.d_hitems.p, P.n_hist, P.cn, h->gamma, make_weights(h->win_sigma),
+                    (float)h->l2hys, h->d_hist.p, st);
+        (*launches)++;
+    }
+    if (h->timing) cudaEventRecord(h->ev[3], st);
+    if (ndet > 0 && P.n_svm) {
+        SvmParams sp; memset(&sp, 0, sizeof sp);
+        sp.win_bx = win_bx(h); sp.win_by = win_by(h);
+        sp.stride_bx = h->win_stride_x / kCell; sp.stride_by = h->win_stride_y / kCell;
+        sp.ndet = ndet;
+        for (int d = 0; d < ndet; d++) { sp.det[d] = h->d_det[slots[d]].p; sp.bias[d] = h->bias[slots[d]]; }
+        sp.thresh = thresh; sp.scores = d_scores; sp.score_plane = P.score_floats;
+        sp.cand = reinterpret_cast<Candidate*>(h->d_cand.p + 16);
+        sp.cand_count = reinterpret_cast<unsigned int*>(h->d_cand.p);
+        sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
+        launch_svm(P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, st);
+        (*launches)++;
+    }
+    if (h->timing) cudaEventRecord(h->ev[4], st);
+    CK(cudaGetLastError());
+    return HOGB200_OK;
+}
+
+// Bring the candidate list of the finished chunk to the host.  Returns HOGB200_CAPACITY (with *count set) when
+// the device list overflowed and the chunk must be re-run with a larger list.
+int fetch_candidates(hogb200* h, std::vector<Candidate>& out, size_t* count)
+{
+    cudaStream_t st = h->stream;
+    const size_t first = std::min<size_t>(h->cand_cap, 4096);
+    CK(h->h_cand.reserve(16 + h->cand_cap * sizeof(Candidate)));
+    CK(cudaMemcpyAsync(h->h_cand.p, h->d_cand.p, 16 + first * sizeof(Candidate), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const size_t n = *reinterpret_cast<unsigned int*>(h->h_cand.p);
+    *count = n;
+    if (n > h->cand_cap) return HOGB200_CAPACITY;
+    if (n > first) {
+        CK(cudaMemcpyAsync(h->h_cand.p + 16 + first * sizeof(Candidate), h->d_cand.p + 16 + first * sizeof(Candidate),
+                           (n - first) * sizeof(Candidate), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    const Candidate* c = reinterpret_cast<const Candidate*>(h->h_cand.p + 16);
+    out.assign(c, c + n);
+    return HOGB200_OK;
+}
+
+inline bool cand_less(const Candidate& a, const Candidate& b)
+{
+    if (a.level != b.level) return (unsigned)a.level < (unsigned)b.level;   // frame, detector, level
+    if (a.y != b.y) return a.y < b.y;
+    return a.x < b.x;
+}
+
+// ---- cv::groupRectangles(rectList, groupThreshold, eps), objdetect/src/cascadedetect.cpp:64-174 ----------
+// Same result as the reference: classes are the connected components of the SimilarRects relation
+// (objdetect.hpp:121-134), numbered by first appearance (cv::partition, core/operations.hpp:481-569), but the
+// O(N^2) predicate scan is cut down by sorting on x: similar rects differ in x by at most
+// eps*(w_i+h_i)/2, so only a window of the sorted order is examined.
+struct Uf {
+    std::vector<int> p;
+    explicit Uf(int n) : p(n) { for (int i = 0; i < n; i++) p[i] = i; }
+    int find(int a) { while (p[a] != a) { p[a] = p[p[a]]; a = p[a]; } return a; }
+    void unite(int a, int b) { a = find(a); b = find(b); if (a != b) p[std::max(a, b)] = std::min(a, b); }
+};
+
+inline bool similar(const hogb200_rect& r1, const hogb200_rect& r2, double eps)
+{
+    const double delta = eps * (std::min(r1.width, r2.width) + std::min(r1.height, r2.height)) * 0.5;
+    return std::abs(r1.x - r2.x) <= delta && std::abs(r1.y - r2.y) <= delta &&
+           std::abs(r1.x + r1.width - r2.x - r2.width) <= delta &&
+           std::abs(r1.y + r1.height - r2.y - r2.height) <= delta;
+}
+
+void group_rectangles(std::vector<hogb200_rect>& rects, int groupThreshold, double eps)
+{
+    if (groupThreshold <= 0 || rects.empty()) return;
+    const int N = (int)rects.size();
+    std::vector<int> order(N);
+    for (int i = 0; i < N; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return rects[a].x < rects[b].x; });
+    Uf uf(N);
+    for (int a = 0; a < N; a++) {
+        const hogb200_rect& ra = rects[order[a]];
+        const double reach = eps * (ra.width + ra.height) * 0.5;
+        for (int b = a + 1; b < N; b++) {
+            const hogb200_rect& rb = rects[order[b]];
+            if (rb.x - ra.x > reach) break;
+            if (similar(ra, rb, eps)) uf.unite(order[a], order[b]);
+        }
+    }
+    // class labels in order of first appearance (root = smallest member index => first appearance of the class)
+    std::vector<int> label(N, -1);
+    int nclasses = 0;
+    std::vector<int> cls(N);
+    for (int i = 0; i < N; i++) {
+        const int r = uf.find(i);
+        if (label[r] < 0) label[r] = nclasses++;
+        cls[i] = label[r];
+    }
+    std::vector<hogb200_rect> rr(nclasses, hogb200_rect{0, 0, 0, 0});
+    std::vector<int> rw(nclasses, 0);
+    for (int i = 0; i < N; i++) {
+        hogb200_rect& r = rr[cls[i]];
+        r.x += rects[i].x; r.y += rects[i].y; r.width += rects[i].width; r.height += rects[i].height;
+        rw[cls[i]]++;
+    }
+    for (int i = 0; i < nclasses; i++) {
+        const float s = 1.f / rw[i];
+        hogb200_rect r = rr[i];
+        rr[i] = hogb200_rect{(int)lrintf(r.x * s), (int)lrintf(r.y * s), (int)lrintf(r.width * s), (int)lrintf(r.height * s)};
+    }
+    rects.clear();
+    for (int i = 0; i < nclasses; i++) {
+        const hogb200_rect r1 = rr[i];
+        const int n1 = rw[i];
+        if (n1 <= groupThreshold) continue;
+        int j;
+        for (j = 0; j < nclasses; j++) {
+            const int n2 = rw[j];
+            if (j == i || n2 <= groupThreshold) continue;
+            const hogb200_rect r2 = rr[j];
+            const int dx = cvRound(r2.width * eps), dy = cvRound(r2.height * eps);
+            if (r1.x >= r2.x - dx && r1.y >= r2.y - dy && r1.x + r1.width <= r2.x + r2.width + dx &&
+                r1.y + r1.height <= r2.y + r2.height + dy && (n2 > std::max(3, n1) || n1 < 3))
+                break;
+        }
+        if (j == nclasses) rects.push_back(r1);
+    }
+}
+
+// candidates of one (frame, detector), already in (level, y, x) order -> rects (hog.cpp:471-481) [+ grouping :484-487]
+void candidates_to_rects(const hogb200* h, const Plan& P, const Candidate* c, size_t n,
+                         std::vector<hogb200_rect>& rects, std::vector<double>* conf)
+{
+    rects.clear();
+    if (conf) conf->clear();
+    for (size_t i = 0; i < n; i++) {
+        const int lvl = c[i].level & 0xffff;
+        const double scale = P.lv[lvl].scale;
+        hogb200_rect r;
+        r.x = cvRound((double)(c[i].x * h->win_stride_x) * scale);
+        r.y = cvRound((double)(c[i].y * h->win_stride_y) * scale);
+        r.width = cvRound(h->g.win_w * scale);
+        r.height = cvRound(h->g.win_h * scale);
+        rects.push_back(r);
+        if (conf) conf->push_back((double)c[i].score);
+    }
+    if (h->group_threshold > 0) group_rectangles(rects, h->group_threshold, 0.2);
+}
+
+void finish_timing(hogb200* h, const Plan& P, int launches, size_t ncand)
+{
+    h->last = hogb200_timings{};
+    h->last.kernel_launches = launches;
+    h->last.pyramid_pixels = P.pyr_pixels; h->last.blocks = P.nblocks; h->last.windows = P.nwindows;
+    h->last.candidates = (long long)ncand;
+    if (!h->timing) return;
+    cudaEventSynchronize(h->ev[5]);
+    cudaEventElapsedTime(&h->last.upload_ms, h->ev[0], h->ev[1]);
+    cudaEventElapsedTime(&h->last.resize_ms, h->ev[1], h->ev[2]);
+    cudaEventElapsedTime(&h->last.hist_ms, h->ev[2], h->ev[3]);
+    cudaEventElapsedTime(&h->last.svm_ms, h->ev[3], h->ev[4]);
+    cudaEventElapsedTime(&h->last.download_ms, h->ev[4], h->ev[5]);
+    cudaEventElapsedTime(&h->last.total_ms, h->ev[0], h->ev[5]);
+}
+
+}  // namespace
+
+// =============================================================================== C ABI
+extern "C" {
+
+const char* hogb200_last_error(void) { return g_err.c_str(); }
+const char* hogb200_version(void) { return "hogb200 0.1 (sm_100a)"; }
+
+int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
+{
+    if (!out) return fail(HOGB200_BAD_ARG, "out is null");
+    *out = nullptr;
+    hogb200_geom g = {64, 128, 16, 16, 8, 8, 8, 8, 9};
+    if (geom) g = *geom;
+    // ctor asserts, hog.cpp:252-264
+    if (g.block_stride_w <= 0 || g.block_stride_h <= 0 || g.cell_w <= 0 || g.cell_h <= 0 || g.block_w <= 0 || g.block_h <= 0)
+        return fail(HOGB200_BAD_ARG, "sizes must be positive");
+    if ((g.win_w - g.block_w) % g.block_stride_w != 0 || (g.win_h - g.block_h) % g.block_stride_h != 0)
+        return fail(HOGB200_BAD_ARG, "(win_size - block_size) % block_stride != 0");
+    if (g.block_w % g.cell_w != 0 || g.block_h % g.cell_h != 0) return fail(HOGB200_BAD_ARG, "block_size % cell_size != 0");
+    if (g.block_stride_w * 2 != g.block_w || g.block_stride_h * 2 != g.block_h)
+        return fail(HOGB200_BAD_ARG, "block_stride must equal block_size / 2");
+    if (g.cell_w != g.cell_h) return fail(HOGB200_BAD_ARG, "cells must be square");
+    if (g.block_w != kBlock || g.block_h != kBlock || g.cell_w != kCell || g.nbins != kBins)
+        return fail(HOGB200_UNSUPPORTED, "only block 16x16 / cell 8x8 / 9 bins is supported (cudaobjdetect.hpp:89-93)");
+    if (g.win_w < kBlock || g.win_h < kBlock) return fail(HOGB200_BAD_ARG, "window smaller than a block");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return fail(HOGB200_CUDA_ERROR, "no CUDA device: hogb200 has no CPU fallback");
+    }
+    if (device < 0 || device >= ndev) return fail(HOGB200_BAD_ARG, "bad device index");
+    hogb200* h = new hogb200();
+    h->device = device; h->g = g;
+    h->win_stride_x = g.block_stride_w; h->win_stride_y = g.block_stride_h;   // hog.cpp:246
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+        e = cudaEventCreateWithFlags(&h->up_done[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->fr_done[i], cudaEventDisableTiming);
+    }
+    for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&h->ev[i]);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        hogb200_destroy(h);
+        return fail(HOGB200_CUDA_ERROR, std::string("create: ") + cudaGetErrorString(e));
+    }
+    h->stream = h->own_stream;
+    *out = h;
+    return HOGB200_OK;
+}
+
+void hogb200_destroy(hogb200_t* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (int i = 0; i < kMaxDet; i++) h->d_det[i].release();
+    h->d_frame[0].release(); h->d_frame[1].release(); h->d_pyr.release(); h->d_hist.release();
+    h->d_scores.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
+    for (Plan* P : {&h->plan, &h->plan1}) {
+        P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
+        P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();
+    }
+    for (int i = 0; i < 2; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
+    for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    delete h;
+}
+
+int hogb200_set_stream(hogb200_t* h, void* s)
+{
+    if (!h) return fail(HOGB200_BAD_ARG, "null handle");
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    h->stream = s ? (cudaStream_t)s : h->own_stream;
+    return HOGB200_OK;
+}
+
+#define H_OR_FAIL if (!h) return fail(HOGB200_BAD_ARG, "null handle")
+int hogb200_set_win_sigma(hogb200_t* h, double v) { H_OR_FAIL; h->win_sigma = v; return HOGB200_OK; }
+double hogb200_get_win_sigma(const hogb200_t* h) { return h->win_sigma >= 0 ? h->win_sigma : (h->g.block_w + h->g.block_h) / 8.0; }
+int hogb200_set_l2hys_threshold(hogb200_t* h, double v) { H_OR_FAIL; h->l2hys = v; return HOGB200_OK; }
+double hogb200_get_l2hys_threshold(const hogb200_t* h) { return h->l2hys; }
+int hogb200_set_gamma_correction(hogb200_t* h, int v) { H_OR_FAIL; h->gamma = v != 0; return HOGB200_OK; }
+int hogb200_get_gamma_correction(const hogb200_t* h) { return h->gamma; }
+int hogb200_set_num_levels(hogb200_t* h, int v) { H_OR_FAIL; h->nlevels = v; return HOGB200_OK; }
+int hogb200_get_num_levels(const hogb200_t* h) { return h->nlevels; }
+int hogb200_set_hit_threshold(hogb200_t* h, double v) { H_OR_FAIL; h->hit_threshold = v; return HOGB200_OK; }
+double hogb200_get_hit_threshold(const hogb200_t* h) { return h->hit_threshold; }
+int hogb200_set_win_stride(hogb200_t* h, int sx, int sy)
+{
+    H_OR_FAIL;
+    if (sx <= 0 || sy <= 0) return fail(HOGB200_BAD_ARG, "win_stride must be positive");
+    h->win_stride_x = sx; h->win_stride_y = sy;     // divisibility is checked by the work calls, as hog.cpp:341,497 do
+    return HOGB200_OK;
+}
+void hogb200_get_win_stride(const hogb200_t* h, int* sx, int* sy) { if (sx) *sx = h->win_stride_x; if (sy) *sy = h->win_stride_y; }
+int hogb200_set_scale_factor(hogb200_t* h, double v) { H_OR_FAIL; h->scale0 = v; return HOGB200_OK; }
+double hogb200_get_scale_factor(const hogb200_t* h) { return h->scale0; }
+int hogb200_set_group_threshold(hogb200_t* h, int v) { H_OR_FAIL; h->group_threshold = v; return HOGB200_OK; }
+int hogb200_get_group_threshold(const hogb200_t* h) { return h->group_threshold; }
+int hogb200_set_descriptor_format(hogb200_t* h, int v)
+{
+    H_OR_FAIL;
+    if (v != HOGB200_DESCR_FORMAT_COL_BY_COL && v != HOGB200_DESCR_FORMAT_ROW_BY_ROW)
+        return fail(HOGB200_BAD_ARG, "Unknown descriptor format");
+    h->descr_format = v; return HOGB200_OK;
+}
+int hogb200_get_descriptor_format(const hogb200_t* h) { return h->descr_format; }
+size_t hogb200_get_descriptor_size(const hogb200_t* h) { return (size_t)win_bx(h) * win_by(h) * kHist; }
+size_t hogb200_get_block_histogram_size(const hogb200_t*) { return kHist; }
+int hogb200_enable_timing(hogb200_t* h, int on) { H_OR_FAIL; h->timing = on != 0; return HOGB200_OK; }
+int hogb200_last_timings(const hogb200_t* h, hogb200_timings* out) { if (!h || !out) return fail(HOGB200_BAD_ARG, "null"); *out = h->last; return HOGB200_OK; }
+
+int hogb200_set_svm_detector(hogb200_t* h, int slot, const float* coeffs, size_t n)
+{
+    H_OR_FAIL;
+    if (slot < 0 || slot >= kMaxDet) return fail(HOGB200_BAD_ARG, "bad detector slot");
+    if (use_device(h)) return HOGB200_CUDA_ERROR;
+    if (n == 0) { CK(cudaStreamSynchronize(h->stream)); h->have_det[slot] = false; return HOGB200_OK; }
+    const size_t ds = hogb200_get_descriptor_size(h);
+    if (!coeffs || (n != ds && n != ds + 1))
+        return fail(HOGB200_BAD_ARG, "detector.cols must be descriptor_size or descriptor_size + 1 (hog.cpp:301)");
+    // reorder blocks from column-major (public / CPU order) to row-major (hog.cpp:303-317)
+    const int bw = win_bx(h), bh = win_by(h);
+    std::vector<float> re(ds);
+    for (int i = 0; i < bh; i++)
+        for (int j = 0; j < bw; j++)
+            memcpy(&re[(size_t)(i * bw + j) * kHist], coeffs + (size_t)(j * bh + i) * kHist, kHist * sizeof(float));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(h->d_det[slot].reserve(ds + 4));
+    CK(cudaMemcpy(h->d_det[slot].p, re.data(), ds * sizeof(float), cudaMemcpyHostToDevice));
+    h->bias[slot] = n > ds ? coeffs[ds] : 0.f;      // hog.cpp:320
+    h->have_det[slot] = true;
+    return HOGB200_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int check_work_params(const hogb200* h)
+{
+    if (h->win_stride_x % h->g.block_stride_w != 0 || h->win_stride_y % h->g.block_stride_h != 0)
+        return fail(HOGB200_BAD_ARG, "win_stride must be a multiple of block_stride (hog.cpp:341)");
+    return HOGB200_OK;
+}
+
+// One frame through the pipeline; candidates come back sorted by (detector, level, y, x).
+int run_single(hogb200* h, Plan& P, const hogb200_image* img, bool single, int ndet, const int* slots,
+               float thresh, float* d_scores, std::vector<Candidate>& cands)
+{
+    int rc;
+    if ((rc = check_image(img))) return rc;
+    if ((rc = check_work_params(h))) return rc;
+    if ((rc = use_device(h))) return rc;
+    if ((rc = build_plan(h, P, img->width, img->height, img->channels, single))) return rc;
+    if (ndet > 0 && win_bx(h) != 7 && win_bx(h) != 5)
+        return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows 64 (7 blocks) or 48 (5 blocks) pixels wide");
+    if (ndet > 0 && win_by(h) > 15) return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows up to 128 pixels high");
+    size_t cap = std::max<size_t>(h->cand_cap, 1 << 16);
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if ((rc = ensure_cand(h, cap))) return rc;
+        cudaStream_t st = h->stream;
+        int launches = 0;
+        if (h->timing) cudaEventRecord(h->ev[0], st);
+        CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
+        FrameRef f;
+        if ((rc = stage_frame(h, img, 0, st, f))) return rc;
+        if ((rc = queue_frame(h, P, f, ndet, slots, thresh, d_scores, 0, &launches))) return rc;
+        size_t n = 0;
+        rc = fetch_candidates(h, cands, &n);
+        if (h->timing) cudaEventRecord(h->ev[5], st);
+        if (rc == HOGB200_CAPACITY && attempt == 0) { cap = (size_t)P.nwindows * std::max(ndet, 1) + 16; continue; }
+        if (rc) return rc;
+        finish_timing(h, P, launches, n);
+        break;
+    }
+    std::sort(cands.begin(), cands.end(), cand_less);
+    return HOGB200_OK;
+}
+
+template <typename T>
+int emit(const std::vector<T>& v, T* out, size_t capacity, size_t* count)
+{
+    if (count) *count = v.size();
+    if (v.size() > capacity) return fail(HOGB200_CAPACITY, "output capacity too small");
+    if (!v.empty() && !out) return fail(HOGB200_BAD_ARG, "output pointer is null");
+    if (!v.empty()) memcpy(out, v.data(), v.size() * sizeof(T));
+    return HOGB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hogb200_detect(hogb200_t* h, const hogb200_image* img, hogb200_point* hits, double* conf, size_t capacity, size_t* count)
+{
+    H_OR_FAIL;
+    if (count) *count = 0;
+    if (!h->have_det[0]) { int rc = check_image(img); return rc ? rc : check_work_params(h); }   // hog.cpp:343-345
+    std::vector<Candidate> c;
+    const int slot0 = 0;
+    int rc = run_single(h, h->plan1, img, true, 1, &slot0, (float)h->hit_threshold, nullptr, c);
+    if (rc) return rc;
+    std::vector<hogb200_point> pts; std::vector<double> cf;
+    for (const Candidate& k : c) {
+        if (conf && !((double)k.score >= h->hit_threshold)) continue;        // hog.cpp:405: float score vs double threshold
+        pts.push_back(hogb200_point{k.x * h->win_stride_x, k.y * h->win_stride_y});
+        cf.push_back((double)k.score);
+    }
+    rc = emit(pts, hits, capacity, count);
+    if (rc == HOGB200_OK && conf && !cf.empty()) memcpy(conf, cf.data(), cf.size() * sizeof(double));
+    return rc;
+}
+
+int hogb200_detect_multiscale_slot(hogb200_t* h, int slot, const hogb200_image* img, hogb200_rect* found, double* conf,
+                                   size_t capacity, size_t* count)
+{
+    H_OR_FAIL;
+    if (count) *count = 0;
+    if (slot < 0 || slot >= kMaxDet) return fail(HOGB200_BAD_ARG, "bad detector slot");
+    if (conf && h->group_threshold != 0)
+        return fail(HOGB200_BAD_ARG, "confidences require group_threshold == 0 (hog.cpp:422)");
+    if (!h->have_det[slot]) { int rc = check_image(img); return rc ? rc : check_work_params(h); }
+    std::vector<Candidate> c;
+    int rc = run_single(h, h->plan, img, false, 1, &slot, (float)h->hit_threshold, nullptr, c);
+    if (rc) return rc;
+    if (conf) {   // confidence path compares the float score with the double threshold (hog.cpp:405)
+        c.erase(std::remove_if(c.begin(), c.end(), [&](const Candidate& k) { return !((double)k.score >= h->hit_threshold); }), c.end());
+    }
+    std::vector<hogb200_rect> rects; std::vector<double> cf;
+    candidates_to_rects(h, h->plan, c.data(), c.size(), rects, conf ? &cf : nullptr);
+    rc = emit(rects, found, capacity, count);
+    if (rc == HOGB200_OK && conf && !cf.empty()) memcpy(conf, cf.data(), cf.size() * sizeof(double));
+    return rc;
+}
+
+int hogb200_detect_multiscale(hogb200_t* h, const hogb200_image* img, hogb200_rect* found, double* conf, size_t capacity, size_t* count)
+{
+    return hogb200_detect_multiscale_slot(h, 0, img, found, conf, capacity, count);
+}
+
+int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, int nframes, int nslots,
+                                    hogb200_rect* found, size_t capacity, size_t* offsets)
+{
+    H_OR_FAIL;
+    if (nframes < 0 || !offsets || (nframes > 0 && !frames)) return fail(HOGB200_BAD_ARG, "bad batch arguments");
+    if (nslots < 1 || nslots > kMaxDet) return fail(HOGB200_BAD_ARG, "bad nslots");
+    for (int d = 0; d < nslots; d++) if (!h->have_det[d]) return fail(HOGB200_BAD_ARG, "detector slot not set");
+    int rc;
+    if ((rc = check_work_params(h))) return rc;
+    if ((rc = use_device(h))) return rc;
+    int slots[kMaxDet] = {0, 1, 2, 3};
+    std::vector<hogb200_rect> all; all.reserve(1024);
+    offsets[0] = 0;
+    size_t out_idx = 0;
+    int total_launches = 0;
+    const int kChunk = 64;
+    std::vector<Candidate> c; std::vector<hogb200_rect> rects;
+    cudaStream_t st = h->stream, cs = h->copy_stream;
+    if (h->timing) cudaEventRecord(h->ev[0], st);
+    for (int i = 0; i < nframes; i++) if ((rc = check_image(&frames[i]))) return rc;
+    int f0 = 0;
+    while (f0 < nframes) {
+        // a chunk = consecutive frames of one shape (they share a plan), at most kChunk
+        int nf = 1;
+        while (f0 + nf < nframes && nf < kChunk && frames[f0 + nf].width == frames[f0].width &&
+               frames[f0 + nf].height == frames[f0].height && frames[f0 + nf].channels == frames[f0].channels) nf++;
+        const hogb200_image* fr = &frames[f0];
+        if ((rc = build_plan(h, h->plan, fr->width, fr->height, fr->channels, false))) return rc;
+        Plan& P = h->plan;
+        size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
+        for (int attempt = 0; attempt < 2; attempt++) {
+            if ((rc = ensure_cand(h, cap))) return rc;
+            CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
+            for (int i = 0; i < nf; i++) {
+                const hogb200_image* im = fr + i;
+                const int b = i & 1;
+                FrameRef f;
+                if (!im->on_device) {
+                    // double-buffered upload on the copy stream, overlapping the previous frame's kernels
+                    CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
+                    if ((rc = stage_frame(h, im, b, cs, f))) return rc;
+                    CK(cudaEventRecord(h->up_done[b], cs));
+                    CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
+                } else {
+                    if ((rc = stage_frame(h, im, b, st, f))) return rc;
+                }
+                if ((rc = queue_frame(h, P, f, nslots, slots, (float)h->hit_threshold, nullptr, i << 20, &total_launches))) return rc;
+                CK(cudaEventRecord(h->fr_done[b], st));
+            }
+            size_t n = 0;
+            rc = fetch_candidates(h, c, &n);
+            if (rc == HOGB200_CAPACITY && attempt == 0) { cap = (size_t)P.nwindows * nslots * nf + 16; continue; }
+            if (rc) return rc;
+            break;
+        }
+        std::sort(c.begin(), c.end(), cand_less);
+        size_t pos = 0;
+        for (int i = 0; i < nf; i++)
+            for (int d = 0; d < nslots; d++) {
+                const int key = (i << 20) | (d << 16);
+                size_t e = pos;
+                while (e < c.size() && (c[e].level & ~0xffff) == key) e++;
+                candidates_to_rects(h, P, c.data() + pos, e - pos, rects, nullptr);
+                pos = e;
+                all.insert(all.end(), rects.begin(), rects.end());
+                offsets[++out_idx] = all.size();
+            }
+        f0 += nf;
+    }
+    if (h->timing) cudaEventRecord(h->ev[5], st);
+    finish_timing(h, h->plan, total_launches, all.size());
+    size_t cnt = 0;
+    return emit(all, found, capacity, &cnt);
+}
+
+}  // extern "C"
+
+#include "people_detector.inc"
+
+extern "C" {
+
+int hogb200_default_people_detector(int win_w, int win_h, const float** coeffs, size_t* n)
+{
+    if (!coeffs || !n) return fail(HOGB200_BAD_ARG, "null output");
+    if (win_w == 64 && win_h == 128) { *coeffs = reinterpret_cast<const float*>(kPeople64x128); *n = 3781; return HOGB200_OK; }
+    if (win_w == 48 && win_h == 96) { *coeffs = reinterpret_cast<const float*>(kPeople48x96); *n = 1981; return HOGB200_OK; }
+    return fail(HOGB200_BAD_ARG, "getDefaultPeopleDetector: win_size must be 64x128 or 48x96 (hog.cpp:328)");
+}
+
+int hogb200_levels(const hogb200_t* h, int width, int height, double* scales, int* widths, int* heights,
+                   size_t capacity, size_t* count)
+{
+    H_OR_FAIL;
+    std::vector<double> sc;
+    enumerate_levels(width, height, h->g.win_w, h->g.win_h, h->scale0, h->nlevels, sc);
+    if (count) *count = sc.size();
+    if (sc.size() > capacity) return fail(HOGB200_CAPACITY, "output capacity too small");
+    for (size_t i = 0; i < sc.size(); i++) {
+        if (scales) scales[i] = sc[i];
+        if (widths) widths[i] = cvRound(width / sc[i]);
+        if (heights) heights[i] = cvRound(height / sc[i]);
+    }
+    return HOGB200_OK;
+}
+
+int hogb200_enumerate_levels(int width, int height, int win_w, int win_h, double scale0, int nlevels,
+                             double* scales, int* widths, int* heights, size_t capacity, size_t* count)
+{
+    std::vector<double> sc;
+    enumerate_levels(width, height, win_w, win_h, scale0, nlevels, sc);
+    if (count) *count = sc.size();
+    if (sc.size() > capacity) return fail(HOGB200_CAPACITY, "output capacity too small");
+    for (size_t i = 0; i < sc.size(); i++) {
+        if (scales) scales[i] = sc[i];
+        if (widths) widths[i] = cvRound(width / sc[i]);
+        if (heights) heights[i] = cvRound(height / sc[i]);
+    }
+    return HOGB200_OK;
+}
+
+int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold, double eps, size_t* count)
+{
+    if (n && !rects) return fail(HOGB200_BAD_ARG, "null rects");
+    std::vector<hogb200_rect> v(rects, rects + n);
+    group_rectangles(v, group_threshold, eps);
+    if (!v.empty()) memcpy(rects, v.data(), v.size() * sizeof(hogb200_rect));
+    if (count) *count = v.size();
+    return HOGB200_OK;
+}
+
+int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h, uint8_t* out)
+{
+    H_OR_FAIL;
+    int rc;
+    if ((rc = check_image(img))) return rc;
+    if (dst_w <= 0 || dst_h <= 0 || !out) return fail(HOGB200_BAD_ARG, "bad destination");
+    if ((rc = use_device(h))) return rc;
+    cudaStream_t st = h->stream;
+    const int cn = img->channels, W = img->width, H = img->height;
+    FrameRef f;
+    if ((rc = stage_frame(h, img, 0, st, f))) return rc;
+    const size_t row = (size_t)dst_w * cn;
+    if (dst_w == W && dst_h == H) {            // resize.cpp:3745-3750: plain copy
+        CK(cudaMemcpy2DAsync(out, row, f.dev, f.pitch, row, H, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return HOGB200_OK;
+    }
+    LevelDesc D; memset(&D, 0, sizeof D);
+    D.w = dst_w; D.h = dst_h; D.pitch = (int)align_up(row, 64);
+    D.mode = is_exact_half(W, H, dst_w, dst_h) ? 2 : 1;
+    std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
+    if (D.mode == 1) { resize_table(W, dst_w, true, xt); resize_table(H, dst_h, false, yt); }
+    const int tw = cn == 4 ? 32 : 128;
+    for (int y = 0; y < dst_h; y += 8) for (int x = 0; x < dst_w; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
+    DevBuf<uint8_t> d_out; DevBuf<LevelDesc> d_lv; DevBuf<ResizeCoef> d_xt, d_yt; DevBuf<ResizeItem> d_it;
+    cudaError_t e = d_out.reserve((size_t)D.pitch * dst_h + 64);
+    D.img = d_out.p;
+    if (e == cudaSuccess) e = d_lv.reserve(1);
+    if (e == cudaSuccess) e = d_xt.reserve(xt.size() + 1);
+    if (e == cudaSuccess) e = d_yt.reserve(yt.size() + 1);
+    if (e == cudaSuccess) e = d_it.reserve(items.size() + 1);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_lv.p, &D, sizeof D, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && !xt.empty()) e = cudaMemcpyAsync(d_xt.p, xt.data(), xt.size() * sizeof(ResizeCoef), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && !yt.empty()) e = cudaMemcpyAsync(d_yt.p, yt.data(), yt.size() * sizeof(ResizeCoef), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_it.p, items.data(), items.size() * sizeof(ResizeItem), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        launch_resize(f.dev, f.pitch, W, H, cn, d_lv.p, d_xt.p, d_yt.p, d_it.p, (int)items.size(), st);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy2DAsync(out, row, d_out.p, D.pitch, row, dst_h, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st); else cudaStreamSynchronize(st);
+    d_out.release(); d_lv.release(); d_xt.release(); d_yt.release(); d_it.release();
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(HOGB200_CUDA_ERROR, std::string("resize: ") + cudaGetErrorString(e)); }
+    return HOGB200_OK;
+}
+
+int hogb200_block_histograms(hogb200_t* h, const hogb200_image* img, float* out, size_t capacity_floats,
+                             int* blocks_x, int* blocks_y)
+{
+    H_OR_FAIL;
+    std::vector<Candidate> c;
+    int rc = run_single(h, h->plan1, img, true, 0, nullptr, 0.f, nullptr, c);
+    if (rc) return rc;
+    const LevelHost& L = h->plan1.lv[0];
+    if (blocks_x) *blocks_x = L.nbx;
+    if (blocks_y) *blocks_y = L.nby;
+    const size_t n = (size_t)L.nbx * L.nby * kHist;
+    if (n > capacity_floats) return fail(HOGB200_CAPACITY, "output capacity too small");
+    if (n) {
+        if (!out) return fail(HOGB200_BAD_ARG, "null output");
+        CK(cudaMemcpyAsync(out, h->d_hist.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return HOGB200_OK;
+}
+
+int hogb200_window_scores(hogb200_t* h, int slot, const hogb200_image* img, float* out, size_t capacity_floats,
+                          int* wins_x, int* wins_y)
+{
+    H_OR_FAIL;
+    if (slot < 0 || slot >= kMaxDet || !h->have_det[slot]) return fail(HOGB200_BAD_ARG, "detector slot not set");
+    int rc;
+    if ((rc = check_image(img))) return rc;
+    if ((rc = check_work_params(h))) return rc;
+    if ((rc = use_device(h))) return rc;
+    if ((rc = build_plan(h, h->plan1, img->width, img->height, img->channels, true))) return rc;
+    const LevelHost& L = h->plan1.lv[0];
+    if (wins_x) *wins_x = L.nwx;
+    if (wins_y) *wins_y = L.nwy;
+    const size_t n = (size_t)L.nwx * L.nwy;
+    if (n > capacity_floats) return fail(HOGB200_CAPACITY, "output capacity too small");
+    if (!n) return HOGB200_OK;
+    if (!out) return fail(HOGB200_BAD_ARG, "null output");
+    CK(cudaStreamSynchronize(h->stream));
+    CK(h->d_scores.reserve(n + 16));
+    std::vector<Candidate> c;
+    rc = run_single(h, h->plan1, img, true, 1, &slot, INFINITY, h->d_scores.p, c);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out, h->d_scores.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return HOGB200_OK;
+}
+
+int hogb200_compute(hogb200_t* h, const hogb200_image* img, float* out, size_t capacity_floats, int out_on_device,
+                    size_t* nwindows)
+{
+    H_OR_FAIL;
+    if (nwindows) *nwindows = 0;
+    std::vector<Candidate> c;
+    int rc = run_single(h, h->plan1, img, true, 0, nullptr, 0.f, nullptr, c);
+    if (rc) return rc;
+    const LevelHost& L = h->plan1.lv[0];
+    const size_t nw = (size_t)L.nwx * L.nwy, ds = hogb200_get_descriptor_size(h);
+    if (nwindows) *nwindows = nw;
+    if (nw * ds > capacity_floats) return fail(HOGB200_CAPACITY, "output capacity too small");
+    if (!nw) return HOGB200_OK;
+    if (!out) return fail(HOGB200_BAD_ARG, "null output");
+    float* d_out = out;
+    if (!out_on_device) { CK(h->d_desc.reserve(nw * ds + 16)); d_out = h->d_desc.p; }
+    launch_extract(h->plan1.d_levels.p, L.nwx, L.nwy, h->d_hist.p, win_bx(h), win_by(h), h->win_stride_x / kCell,
+                   h->win_stride_y / kCell, h->descr_format == HOGB200_DESCR_FORMAT_COL_BY_COL, d_out, h->stream);
+    CK(cudaGetLastError());
+    if (!out_on_device) CK(cudaMemcpyAsync(out, d_out, nw * ds * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return HOGB200_OK;
+}
+
+}  // extern "C"

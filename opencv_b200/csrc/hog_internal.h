@@ -1,0 +1,87 @@
+// hog_internal.h -- structures shared by the host pipeline (hog_host.cu) and the sm_100a kernels.
+//
+// Geometry is fixed to what the north-star scope names (and what cudaobjdetect.hpp:89-93 documents as
+// supported): block 16x16, cell 8x8, block stride 8x8, 9 bins -> 36 floats per block.  The window size
+// (64x128, 48x96, ...) and the window stride (a multiple of 8) are run-time parameters.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace hogk {
+
+constexpr int kCell = 8;
+constexpr int kBlock = 16;
+constexpr int kBins = 9;
+constexpr int kHist = 36;            // floats per block histogram
+constexpr int kMaxLevels = 256;
+constexpr int kMaxDet = 4;
+
+// One pyramid level of one frame.  Lives in device memory (array indexed by level).
+struct LevelDesc {
+    const uint8_t* img;   // level image (level 0 may alias the caller's frame)
+    int pitch;            // bytes
+    int w, h;             // pixels
+    int nbx, nby;         // block grid: (w-16)/8+1, (h-16)/8+1 (0 if smaller than a block)
+    int nwx, nwy;         // window grid for the current win size / stride
+    long long hist_off;   // float offset of this level's [nby][nbx][36] plane in the hist buffer
+    long long score_off;  // float offset of this level's [nwy][nwx] plane in the score buffer
+    int xtab_off, ytab_off;  // offsets into the resize coefficient tables (entries)
+    int mode;             // 0 = alias/copy of base, 1 = bilinear, 2 = exact-2x area
+    int pad;
+};
+
+// resize coefficient table entry (one per destination column / row of a level):
+// ofs = source index (column or row; rows NOT yet clipped, see resize.cpp:1821-1825),
+// c0/c1 = 11-bit fixed-point weights (resize.cpp:3647-3655)
+struct ResizeCoef { int ofs; short c0, c1; };
+
+// work item of the fused gradient+histogram kernel: a strip of block rows x a tile of block columns
+struct HistItem { short level; short bx0; short by0; short nby; };   // nby = block rows in this strip
+// work item of the SVM kernel: a tile of windows of one level
+struct SvmItem { short level; short wx0; short wy0; short pad; };
+// work item of the resize kernel: 8 destination rows x a span of columns
+struct ResizeItem { short level; short x0; short y0; short pad; };
+
+// separable block window: vertical (or horizontal) weight of pixel offset i in [0,16) for cell 0 / cell 1 of
+// the block: gauss(i) * bilinear cell weight (HOGCache::init, objdetect/src/hog.cpp:653-839)
+struct BlockWeights { float a0[16]; float a1[16]; };
+
+// x,y = window index (not pixels); level = level | det << 16 | frame-in-chunk << 20
+struct Candidate { int level; int x; int y; float score; };
+
+// ---- kernel launchers (defined in the .cu files) ----------------------------------------------------
+void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
+                   const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
+                   const ResizeItem* d_items, int nitems, cudaStream_t st);
+
+// base/base_pitch: the frame itself, used for levels whose LevelDesc::img is null (level 0 aliases the frame)
+void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels, const HistItem* d_items,
+                 int nitems, int cn, int gamma, const BlockWeights& bw, float l2hys, float* d_hist,
+                 cudaStream_t st);
+
+struct SvmParams {
+    int win_bx, win_by;        // window size in blocks (7 x 15)
+    int stride_bx, stride_by;  // window stride in blocks
+    int ndet;                  // detectors scored in this pass
+    const float* det[kMaxDet]; // reordered (row-major blocks) coefficients, win_by*win_bx*36 floats each
+    float bias[kMaxDet];
+    float thresh;              // hit threshold
+    float* scores;             // optional dense output (nullptr = none); detector d at + d*score_plane
+    long long score_plane;
+    Candidate* cand;           // compacted hits of all frames / detectors of a chunk
+    unsigned int* cand_count;  // one counter
+    unsigned int cand_cap;
+    int tag;                   // OR-ed into Candidate::level: frame-in-chunk << 20 (detector goes to bits 16..19)
+};
+void launch_svm(const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
+                const SvmParams& p, cudaStream_t st);
+int svm_tile_wx();   // tile geometry the host uses to build SvmItems
+int svm_tile_wy();
+
+void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_hist, int win_bx, int win_by,
+                    int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);
+
+int hist_tile_blocks_x();   // blocks per tile in x (29)
+int hist_strip_blocks_y();  // block rows per strip
+
+}  // namespace hogk

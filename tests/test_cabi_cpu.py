@@ -1,0 +1,78 @@
+"""CPU-side checks of the product library: it loads, exports every symbol include/hogb200.h declares, fails loudly
+without a GPU, and its host-only logic (level enumeration, groupRectangles) equals the oracle's."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from _oracle import Port, Ref
+from opencv_b200 import HOG, HogError, load_library, lib_path
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "hogb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(hogb200_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 38
+    L = C.CDLL(lib_path())
+    missing = [n for n in sorted(names) if not hasattr(L, n)]
+    assert not missing, missing
+
+
+def test_create_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(HogError) as e:
+        HOG.create()
+    assert e.value.status == 2 and "no CPU fallback" in str(e.value)
+
+
+def test_default_people_detector_tables():
+    L = load_library()
+    for (w, h, n) in [(64, 128, 3781), (48, 96, 1981)]:
+        p, cnt = C.c_void_p(), C.c_size_t()
+        assert L.hogb200_default_people_detector(w, h, C.byref(p), C.byref(cnt)) == 0
+        assert cnt.value == n
+        d = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(n,))
+        if Ref.available():
+            assert np.array_equal(d, Ref().people_detector(0 if w == 64 else 1))
+    p, cnt = C.c_void_p(), C.c_size_t()
+    assert L.hogb200_default_people_detector(32, 64, C.byref(p), C.byref(cnt)) == 1     # CV_Assert in the reference
+
+
+@pytest.mark.parametrize("shape", [(640, 480), (1920, 1080), (1242, 375), (3840, 2160), (97, 131), (64, 128), (30, 30)])
+def test_level_enumeration_equals_oracle(shape):
+    port = Port()
+    W, H = shape
+    for win in [(64, 128), (48, 96)]:
+        for scale0, nlevels in [(1.05, 64), (1.02, 128), (1.05, 15), (1.0, 64), (0.9, 5), (1.3, 3), (1.05, 1)]:
+            a = HOG.enumerateLevels(W, H, win, scale0, nlevels)
+            b = port.levels(W, H, win, scale0, nlevels)
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y)
+    # Appendix B of SURVEY.md
+    assert len(HOG.enumerateLevels(1920, 1080)[0]) == 44
+    assert len(HOG.enumerateLevels(640, 480)[0]) == 28
+    assert len(HOG.enumerateLevels(3840, 2160)[0]) == 58
+    assert len(HOG.enumerateLevels(1920, 1080, scale0=1.02, nlevels=128)[0]) == 108
+
+
+def test_group_rectangles_equals_oracle():
+    port = Port()
+    rng = np.random.RandomState(1)
+    for n, thr in [(0, 2), (1, 1), (1, 0), (50, 1), (300, 2), (2000, 2), (400, 0), (400, 5), (3000, 3)]:
+        centers = rng.randint(0, 900, size=(max(n // 10, 1), 2))
+        idx = rng.randint(0, len(centers), size=n)
+        wh = rng.choice([64, 67, 71, 74, 78, 128, 135], size=n)
+        r = np.stack([centers[idx, 0] + rng.randint(-12, 13, n), centers[idx, 1] + rng.randint(-12, 13, n),
+                      wh, wh * 2], 1).astype(np.int32).reshape(-1, 4)
+        a = HOG.groupRectangles(r, thr)
+        b = port.group_rectangles(r, thr)
+        assert np.array_equal(a, b), (n, thr)
+        if Ref.available() and n:
+            assert np.array_equal(a, Ref().group_rectangles(r, thr))

@@ -1,0 +1,345 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (libhogb200.so), against the oracle
+(oracle/hog_oracle.c, pinned to the unmodified reference by tests/test_oracle_vs_ref.py) on the same seeded inputs.
+
+Bars (BASELINE.json north_star):
+  * pyramid levels: BIT-EXACT to cv::resize INTER_LINEAR
+  * descriptors / block histograms: within 1e-4 (relative L2 per block and max-abs, values are in [0, 1])
+  * SVM scores: within 1e-3 absolute
+  * hit lists / grouped detection sets: identical, except for windows whose score lies within 1e-3 of the threshold
+"""
+import numpy as np
+import pytest
+
+from _oracle import Port, Ref, synthetic_frame, parts
+
+pytestmark = pytest.mark.gpu
+
+DESC_TOL = 1e-4
+SCORE_TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def port():
+    return Port()
+
+
+@pytest.fixture(scope="module")
+def hog():
+    from opencv_b200 import HOG
+    h = HOG.create()
+    h.setSVMDetector(h.getDefaultPeopleDetector())
+    return h
+
+
+def rel_l2(a, b):
+    return float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-12))
+
+
+# ------------------------------------------------------------------ pyramid
+@pytest.mark.parametrize("cn", [1, 4])
+@pytest.mark.parametrize("shape", [(640, 480), (1242, 375), (321, 243)])
+def test_pyramid_levels_bit_exact(hog, port, cn, shape):
+    W, H = shape
+    img = synthetic_frame(100 + cn, W, H, cn, blur=False)
+    sc, lw, lh = hog.levels(W, H)
+    sizes = sorted(set(zip(lw.tolist(), lh.tolist())) | {(W // 2, H // 2), (W // 3, H // 3), (W - 1, H - 1), (17, 9)})
+    for dw, dh in sizes:
+        got = hog.resize(img, dw, dh)
+        exp = port.resize(img, dw, dh)
+        assert np.array_equal(got, exp), (dw, dh, int(np.abs(got.astype(int) - exp).max()))
+
+
+def test_pyramid_exact_half_and_upscale(hog, port):
+    img = synthetic_frame(7, 480, 270, 4, blur=False)
+    for dw, dh in [(240, 135), (480, 270), (960, 540), (500, 300)]:
+        assert np.array_equal(hog.resize(img, dw, dh), port.resize(img, dw, dh)), (dw, dh)
+
+
+def test_pyramid_1080p_levels_bit_exact(hog, port):
+    """Full BASELINE size, a sample of the 44 levels (the oracle resizes 1080p in milliseconds)."""
+    img = synthetic_frame(5, 1920, 1080, 4)
+    sc, lw, lh = hog.levels(1920, 1080)
+    assert len(sc) == 44
+    for i in [1, 2, 7, 15, 30, 43]:
+        assert np.array_equal(hog.resize(img, int(lw[i]), int(lh[i])), port.resize(img, int(lw[i]), int(lh[i])))
+
+
+def test_pitched_device_input(hog, port):
+    import torch
+    img = synthetic_frame(8, 333, 222, 4, blur=False)
+    big = torch.zeros((240, 400, 4), dtype=torch.uint8, device="cuda")
+    big[5:227, 16:349] = torch.from_numpy(img).cuda()
+    roi = big[5:227, 16:349]                     # a pitched ROI, like a GpuMat sub-matrix
+    assert np.array_equal(hog.resize(roi, 200, 133), port.resize(img, 200, 133))
+    a = hog.blockHistograms(roi)
+    b = hog.blockHistograms(img)
+    assert np.array_equal(a, b)
+
+
+# ------------------------------------------------------------------ block histograms / descriptors
+@pytest.mark.parametrize("cn", [1, 4])
+@pytest.mark.parametrize("shape", [(64, 128), (640, 480), (333, 222), (251, 517), (16, 16), (24, 40)])
+def test_block_histograms(hog, port, cn, shape):
+    W, H = shape
+    img = synthetic_frame(200 + cn + W, W, H, cn)
+    got = hog.blockHistograms(img)
+    exp = port.block_hists(img)
+    assert got.shape == exp.shape
+    assert np.abs(got - exp).max() <= DESC_TOL, float(np.abs(got - exp).max())
+    err = np.linalg.norm(got - exp, axis=2) / np.maximum(np.linalg.norm(exp, axis=2), 1e-6)
+    assert err.max() <= DESC_TOL, float(err.max())
+
+
+def test_block_histograms_noise_and_flat(hog, port):
+    """Unblurred noise (every pixel a strong edge) and a flat image (all gradients zero)."""
+    img = synthetic_frame(3, 320, 240, 4, blur=False)
+    assert np.abs(hog.blockHistograms(img) - port.block_hists(img)).max() <= DESC_TOL
+    flat = np.full((96, 160), 77, np.uint8)
+    got = hog.blockHistograms(flat)
+    assert np.array_equal(got, port.block_hists(flat)) and not np.isnan(got).any()
+
+
+def test_gamma_off_and_sigma(port):
+    from opencv_b200 import HOG
+    from _oracle import DEFAULT_GEOM
+    h = HOG.create()
+    img = synthetic_frame(4, 200, 160, 1)
+    h.setGammaCorrection(False)
+    assert np.abs(h.blockHistograms(img) - port.block_hists(img, dict(DEFAULT_GEOM, gamma=False))).max() <= DESC_TOL
+    h.setGammaCorrection(True); h.setWinSigma(3.0); h.setL2HysThreshold(0.3)
+    assert h.getWinSigma() == 3.0
+    exp = port.block_hists(img, dict(DEFAULT_GEOM, win_sigma=3.0, l2hys=0.3))
+    assert np.abs(h.blockHistograms(img) - exp).max() <= DESC_TOL
+
+
+@pytest.mark.parametrize("cn", [1, 4])
+def test_compute_descriptors_both_formats(hog, port, cn):
+    """HOG::compute vs HOGDescriptor::compute; ROW_BY_ROW is a block permutation of COL_BY_COL
+    (cudaobjdetect/test/test_objdetect.cpp:173-219)."""
+    img = synthetic_frame(31 + cn, 64 * 3, 128 * 2, cn)
+    for ws in [(64, 128), (8, 8), (16, 8)]:
+        hog.setWinStride(ws)
+        hog.setDescriptorFormat(hog.DESCR_FORMAT_COL_BY_COL)
+        col = hog.compute(img)
+        exp = port.compute(img, ws)
+        assert col.shape == exp.shape == (parts(192, 64, ws[0]) * parts(256, 128, ws[1]), 3780)
+        assert np.abs(col - exp).max() <= DESC_TOL
+        hog.setDescriptorFormat(hog.DESCR_FORMAT_ROW_BY_ROW)
+        row = hog.compute(img)
+        perm = row.reshape(-1, 15, 7, 36).transpose(0, 2, 1, 3).reshape(-1, 3780)
+        assert np.array_equal(perm, col)
+    hog.setWinStride((8, 8)); hog.setDescriptorFormat(hog.DESCR_FORMAT_COL_BY_COL)
+
+
+def test_descriptors_vs_unmodified_reference(hog):
+    """Directly against cv::HOGDescriptor::compute of the unmodified reference (when oracle/_ref travelled)."""
+    if not Ref.available():
+        pytest.skip("oracle/_ref not present")
+    ref = Ref()
+    img = ref.rng_fill(0x77, 128, 256, 1)[:, :, 0]     # the Strict test's kind of input
+    got = hog.compute(img)
+    exp = ref.compute(img)
+    assert np.abs(got - exp).max() <= DESC_TOL and rel_l2(got, exp) <= DESC_TOL
+
+
+# ------------------------------------------------------------------ scores / detect
+@pytest.mark.parametrize("cn", [1, 4])
+@pytest.mark.parametrize("shape", [(64, 128), (320, 272), (641, 483), (71, 135)])
+def test_window_scores(hog, port, cn, shape):
+    W, H = shape
+    img = synthetic_frame(300 + cn + W, W, H, cn, silhouettes=2)
+    det = hog.getDefaultPeopleDetector()
+    got = hog.windowScores(img)
+    exp = port.scores(img, det)
+    assert got.shape == exp.shape
+    assert np.abs(got - exp).max() <= SCORE_TOL, float(np.abs(got - exp).max())
+
+
+def test_window_scores_stride16(port):
+    from opencv_b200 import HOG
+    h = HOG.create(); det = h.getDefaultPeopleDetector(); h.setSVMDetector(det)
+    h.setWinStride((16, 24))
+    img = synthetic_frame(9, 400, 300, 1)
+    got = h.windowScores(img)
+    exp = port.scores(img, det, (16, 24))
+    assert got.shape == exp.shape and np.abs(got - exp).max() <= SCORE_TOL
+
+
+def test_daimler_48x96(port):
+    from opencv_b200 import HOG
+    from _oracle import DEFAULT_GEOM
+    h = HOG.create(win_size=(48, 96)); det = h.getDefaultPeopleDetector()
+    assert det.size == 1981 and h.getDescriptorSize() == 1980
+    h.setSVMDetector(det)
+    img = synthetic_frame(10, 300, 260, 1)
+    g = dict(DEFAULT_GEOM, win=(48, 96))
+    assert np.abs(h.windowScores(img) - port.scores(img, det, (8, 8), g)).max() <= SCORE_TOL
+    assert np.abs(h.compute(img) - port.compute(img, (8, 8), g)).max() <= DESC_TOL
+
+
+def _hits_match(got_xy, exp_scores, thr, stride=8):
+    exp_hit = exp_scores >= thr
+    near = np.abs(exp_scores - thr) <= SCORE_TOL
+    got_mask = np.zeros_like(exp_hit)
+    got_mask[got_xy[:, 1] // stride, got_xy[:, 0] // stride] = True
+    bad = (got_mask != exp_hit) & ~near
+    return not bad.any()
+
+
+def test_detect_hits_and_confidences(hog, port):
+    img = synthetic_frame(12, 480, 360, 4, silhouettes=3)
+    det = hog.getDefaultPeopleDetector()
+    exp = port.scores(img, det)
+    thr = float(np.percentile(exp, 90))
+    hog.setHitThreshold(thr)
+    hits = hog.detect(img)
+    assert _hits_match(hits, exp, thr)
+    # row-major order (hog.cpp:373-379)
+    key = hits[:, 1].astype(np.int64) * 100000 + hits[:, 0]
+    assert np.all(np.diff(key) > 0)
+    hits2, conf = hog.detect(img, confidences=True)
+    assert np.array_equal(hits, hits2)
+    assert np.abs(conf - exp[hits2[:, 1] // 8, hits2[:, 0] // 8]).max() <= SCORE_TOL
+    hog.setHitThreshold(0.0)
+
+
+def test_empty_detector_and_small_image(port):
+    from opencv_b200 import HOG, HogError
+    h = HOG.create()
+    img = synthetic_frame(1, 200, 200, 1)
+    assert len(h.detect(img)) == 0 and len(h.detectMultiScale(img)) == 0          # hog.cpp:343-345
+    h.setSVMDetector(h.getDefaultPeopleDetector())
+    small = synthetic_frame(2, 40, 60, 1)                                           # smaller than the window
+    assert len(h.detect(small)) == 0 and len(h.detectMultiScale(small)) == 0
+    assert h.compute(small).shape == (0, 3780)
+    with pytest.raises(HogError):
+        h.detect(np.zeros((100, 100, 3), np.uint8))                                 # CV_8UC3 is not accepted
+    h.setWinStride((12, 8))
+    with pytest.raises(HogError):
+        h.detect(img)                                                               # hog.cpp:341
+    h.setWinStride((8, 8)); h.setGroupThreshold(2)
+    with pytest.raises(HogError):
+        h.detectMultiScale(img, confidences=True)                                   # hog.cpp:422
+    with pytest.raises(HogError):
+        h.setSVMDetector(np.zeros(100, np.float32))                                 # hog.cpp:301
+    with pytest.raises(HogError):
+        HOG.create(win_size=(64, 128), block_size=(16, 16), block_stride=(4, 4))    # hog.cpp:263
+
+
+# ------------------------------------------------------------------ detectMultiScale
+def _set_equal_mod_threshold(hog, port, img, det, hit, group, scale0=1.05, nlevels=64):
+    hog.setHitThreshold(hit); hog.setGroupThreshold(group); hog.setScaleFactor(scale0); hog.setNumLevels(nlevels)
+    got = hog.detectMultiScale(img)
+    exp, _ = port.detect_multiscale(img, det, hit_threshold=hit, scale0=scale0, nlevels=nlevels, group_threshold=group)
+    if np.array_equal(got, exp):
+        return True, got, exp
+    # tolerance clause: candidates whose score is within SCORE_TOL of the threshold may differ.  Recompute the
+    # oracle's answer with those windows forced in / out and accept if either extreme reproduces the GPU set.
+    lo, _ = port.detect_multiscale(img, det, hit_threshold=hit - SCORE_TOL, scale0=scale0, nlevels=nlevels, group_threshold=0)
+    hi, _ = port.detect_multiscale(img, det, hit_threshold=hit + SCORE_TOL, scale0=scale0, nlevels=nlevels, group_threshold=0)
+    hog.setGroupThreshold(0)
+    raw = hog.detectMultiScale(img)
+    hog.setGroupThreshold(group)
+    s_lo = set(map(tuple, lo)); s_hi = set(map(tuple, hi)); s_raw = set(map(tuple, raw))
+    ok = s_hi <= s_raw <= s_lo and len(s_lo - s_hi) > 0
+    return ok, got, exp
+
+
+@pytest.mark.parametrize("cn,shape", [(1, (640, 480)), (4, (640, 480)), (4, (1242, 375)), (1, (300, 400))])
+def test_detect_multiscale_candidates_and_groups(hog, port, cn, shape):
+    W, H = shape
+    img = synthetic_frame(400 + cn + W, W, H, cn, silhouettes=5)
+    det = hog.getDefaultPeopleDetector()
+    for hit, group in [(-1.5, 0), (-1.5, 2), (-2.5, 2), (0.0, 2)]:
+        ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, hit, group)
+        assert ok, (hit, group, len(got), len(exp))
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_detect_multiscale_confidences_and_order(hog, port):
+    img = synthetic_frame(77, 500, 400, 4, silhouettes=4)
+    det = hog.getDefaultPeopleDetector()
+    hog.setHitThreshold(-2.0); hog.setGroupThreshold(0)
+    r, c = hog.detectMultiScale(img, confidences=True)
+    er, ec = port.detect_multiscale(img, det, hit_threshold=-2.0, group_threshold=0)
+    if len(r) == len(er):
+        assert np.array_equal(r, er) and np.abs(c - ec).max() <= SCORE_TOL      # same order: level, row-major
+    else:
+        assert abs(len(r) - len(er)) <= 3
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_sample_settings_tbd(hog, port):
+    """example_gpu_tbd's settings: nlevels=15, hit_threshold=0.45, group 2 (samples/gpu/tbd.cpp:437-442)."""
+    img = synthetic_frame(55, 1242, 375, 4, silhouettes=6)
+    det = hog.getDefaultPeopleDetector()
+    ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, 0.45, 2, 1.05, 15)
+    assert ok
+    ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, -1.0, 2, 1.05, 15)
+    assert ok and len(exp) > 0
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2); hog.setNumLevels(64)
+
+
+def test_two_detectors_and_batch(hog, port):
+    """Pedestrian + (synthetic) vehicle detector scored in one pass; batch API == per-frame API."""
+    rng = np.random.RandomState(5)
+    veh = (rng.randn(3781) * 0.05).astype(np.float32); veh[3780] = -0.5
+    hog.setSVMDetector(veh, slot=1)
+    det = hog.getDefaultPeopleDetector()
+    hog.setHitThreshold(-1.0); hog.setGroupThreshold(2)
+    frames = [synthetic_frame(600 + i, 1242, 375, 4, silhouettes=3) for i in range(5)]
+    out = hog.detectMultiScaleBatch(frames, nslots=2)
+    assert len(out) == 10
+    for i, f in enumerate(frames):
+        assert np.array_equal(out[2 * i], hog.detectMultiScale(f, slot=0))
+        assert np.array_equal(out[2 * i + 1], hog.detectMultiScale(f, slot=1))
+    e0, _ = port.detect_multiscale(frames[0], det, hit_threshold=-1.0, group_threshold=2)
+    e1, _ = port.detect_multiscale(frames[0], veh, hit_threshold=-1.0, group_threshold=2)
+    assert abs(len(out[0]) - len(e0)) <= 1 and abs(len(out[1]) - len(e1)) <= 2
+    import torch
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+    out2 = hog.detectMultiScaleBatch(dev, nslots=2)
+    assert all(np.array_equal(a, b) for a, b in zip(out, out2))
+    hog.setHitThreshold(0.0)
+
+
+def test_dense_candidates_overflow_path(hog, port):
+    """hit_threshold far below every score: every window is a candidate (dense-pyramid stress, config 5 in
+    small): exercises the candidate-list regrow path and the ordering."""
+    img = synthetic_frame(88, 640, 480, 1)
+    hog.setHitThreshold(-100.0); hog.setGroupThreshold(0)
+    r = hog.detectMultiScale(img)
+    sc, lw, lh = hog.levels(640, 480)
+    total = sum(parts(int(w), 64, 8) * parts(int(h), 128, 8) for w, h in zip(lw, lh))
+    assert len(r) == total == 25132
+    er, _ = port.detect_multiscale(img, hog.getDefaultPeopleDetector(), hit_threshold=-100.0, group_threshold=0)
+    assert np.array_equal(r, er)
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_determinism(hog):
+    img = synthetic_frame(99, 800, 600, 4, silhouettes=3)
+    a = hog.blockHistograms(img); b = hog.blockHistograms(img)
+    assert np.array_equal(a, b)
+    assert np.array_equal(hog.windowScores(img), hog.windowScores(img))
+
+
+def test_full_size_1080p_properties(hog, port):
+    """BASELINE config 2 at full size through size-independent properties + a spot check against the oracle."""
+    img = synthetic_frame(2024, 1920, 1080, 4, silhouettes=8)
+    hog.setHitThreshold(-100.0); hog.setGroupThreshold(0)
+    r, c = hog.detectMultiScale(img, confidences=True)
+    assert len(r) == 261558                                    # every window of the 44 levels (Appendix B)
+    sc, lw, lh = hog.levels(1920, 1080)
+    # the level-0 part of the dense list must equal windowScores, in row-major order
+    n0 = parts(1920, 64, 8) * parts(1080, 128, 8)
+    ws = hog.windowScores(img)
+    assert np.array_equal(c[:n0].astype(np.float32).reshape(ws.shape), ws)
+    # spot check one mid-pyramid level against the oracle end to end (resize -> hist -> score)
+    lvl = 20
+    limg = port.resize(img, int(lw[lvl]), int(lh[lvl]))
+    exp = port.scores(limg, hog.getDefaultPeopleDetector())
+    off = sum(parts(int(w), 64, 8) * parts(int(h), 128, 8) for w, h in zip(lw[:lvl], lh[:lvl]))
+    got = c[off:off + exp.size].reshape(exp.shape)
+    assert np.abs(got - exp).max() <= SCORE_TOL
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
