@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+"""bench.py -- HOG detectMultiScale frames/s at 1080p (BASELINE.json metric), one process per GPU.
+
+A step = one pass of the hot path (pyramid -> fused gradient+histogram -> SVM+compaction -> host grouping) over one
+batch of BATCH synthetic 1920x1080 8UC4 frames (BASELINE configs[1]: people detector, nlevels=64, scale 1.05).
+
+  value     frames/s, whole job, frames already resident in HBM when the timed region starts
+  e2e       same metric through the public call with PINNED HOST frames (H2D + result D2H inside the timed region)
+  roofline  fused gradient+histogram kernel: algorithmic bytes ((cn + 2.25) B per pyramid pixel) / its CUDA-event time
+  cpu_baseline  the reference's cv::HOGDescriptor::detectMultiScale (oracle/_ref) on the host cores, bounded sample
+
+`--impl reference` times only the reference CPU implementation (rank 0), same metric and config.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W, H, CN = 1920, 1080, 4
+NLEVELS, SCALE0, HIT, GROUP = 64, 1.05, 0.0, 2
+BATCH = 32                       # frames per step per GPU: 32 x 8.3 MB = 265 MB of distinct input > 126 MB L2
+METRIC = "HOG detectMultiScale frames/s at 1080p"
+UNIT = "frames/s"
+CONFIG = {"workload": "cv::cuda::HOG people detector, synthetic 1920x1080 8UC4, nlevels=64, scale 1.05, "
+                      "hit_threshold 0, group_threshold 2 (BASELINE configs[1])",
+          "frames_per_step_per_gpu": BATCH, "levels": 44, "pyramid_pixels": 21995553, "windows": 261558,
+          "parallelism": "frame-sharded replicas, no collective on the data path",
+          "l2": "inputs larger than L2 (32 distinct frames = 265 MB per step per GPU)"}
+
+
+def make_frames(n, seed0):
+    from _oracle import synthetic_frame
+    base = [synthetic_frame(seed0 + i, W, H, CN, silhouettes=6) for i in range(min(n, 4))]
+    frames = []
+    for i in range(n):                     # distinct bytes per frame without paying n full syntheses
+        f = np.roll(base[i % len(base)], shift=(7 * (i // len(base)), 13 * (i // len(base))), axis=(0, 1)).copy()
+        frames.append(f)
+    return frames
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu = gpu; self.rows = []; self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            c = [x.strip() for x in r.split(",")]
+            if len(c) < 8:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_fps(frames, nthreads=None):
+    """The reference's own CPU path on this box's host cores (oracle/_ref), else the C port.  Test/bench
+    infrastructure only -- never on the product path."""
+    from _oracle import Ref, Port
+    if Ref.available():
+        ref = Ref()
+        if nthreads:
+            ref.set_num_threads(nthreads)
+        det = ref.people_detector(0)
+        cores = ref.get_num_threads()
+        t = []
+        for f in frames:
+            t0 = time.perf_counter()
+            ref.detect_multiscale_stock(f, det, hit_threshold=HIT, win_stride=(8, 8), scale0=SCALE0, nlevels=NLEVELS,
+                                        final_threshold=float(GROUP))
+            t.append(time.perf_counter() - t0)
+        return {"kind": "reference", "cores": cores, "times": t}
+    port = Port()
+    from opencv_b200 import load_library
+    import ctypes as C
+    L = load_library(); p, n = C.c_void_p(), C.c_size_t()
+    L.hogb200_default_people_detector(64, 128, C.byref(p), C.byref(n))
+    det = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(n.value,)).copy()
+    t = []
+    for f in frames:
+        t0 = time.perf_counter()
+        port.detect_multiscale(f, det, hit_threshold=HIT, scale0=SCALE0, nlevels=NLEVELS, group_threshold=GROUP)
+        t.append(time.perf_counter() - t0)
+    return {"kind": "port", "cores": 1, "times": t}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    frames = make_frames(2, 1000)
+    r = cpu_reference_fps([frames[i % 2] for i in range(args.warmup)])          # warm-up
+    r = cpu_reference_fps([frames[i % 2] for i in range(args.steps)])
+    total = sum(r["times"])
+    fps = args.steps / total
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": dict(CONFIG, frames_per_step_per_gpu=1,
+                           note="stock cv::HOGDescriptor::detectMultiScale (CPU, BGR view of the same BGRA frames), "
+                                "1 frame per step"),
+            "cpu_baseline": {"value": fps, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                             "sample": "%d x 1 frame 1920x1080, %s threads (OpenMP parallel_for_ over levels)" % (args.steps, r["cores"])},
+            "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from opencv_b200 import HOG
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    hog = HOG.create(device=local_rank)
+    hog.setSVMDetector(hog.getDefaultPeopleDetector())
+    hog.setNumLevels(NLEVELS); hog.setScaleFactor(SCALE0); hog.setHitThreshold(HIT); hog.setGroupThreshold(GROUP)
+    stream = torch.cuda.Stream()
+    hog.setStream(stream.cuda_stream)
+
+    host = make_frames(BATCH, 1000 + 100 * rank)
+    pinned = [torch.from_numpy(f).pin_memory() for f in host]
+    dev = [p.cuda(non_blocking=False) for p in pinned]
+    pinned_np = [p.numpy() for p in pinned]
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(frames, steps):
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        nrects = 0; launches = 0; cands = 0
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(steps):
+                out = hog.detectMultiScaleBatch(frames)
+                nrects += sum(len(o) for o in out)
+                t = hog.lastTimings(); launches += t["kernel_launches"]; cands += t["candidates"]
+            e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ms], device="cuda"); dist.all_reduce(tms, op=dist.ReduceOp.MAX); ms = float(tms.item())
+        barrier()
+        return ms, nrects, launches, cands
+
+    # ---- device-resident inputs (value)
+    timed(dev, args.warmup)
+    sampler = ClockSampler(local_rank); sampler.start()
+    ms, nrects, launches, _ = timed(dev, args.steps)
+    clocks = sampler.stop()
+    fps = world * BATCH * args.steps / (ms * 1e-3)
+
+    # ---- end to end: pinned host frames through the same public call
+    timed(pinned_np, args.warmup)
+    ms_e2e, nrects_e2e, _, cands_e2e = timed(pinned_np, args.steps)
+    fps_e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
+    h2d = BATCH * W * H * CN
+    d2h = int(16 * ((BATCH + 63) // 64) + 16 * max(cands_e2e, 0) / max(args.steps, 1))
+
+    # ---- per-kernel device times (CUDA events on the launching stream, inside the library) for the roofline
+    hog.enableTiming(True)
+    ks = {"resize_ms": [], "hist_ms": [], "svm_ms": [], "total_ms": []}
+    for i in range(3 + 12):
+        hog.detectMultiScale(dev[i % BATCH])
+        if i >= 3:
+            t = hog.lastTimings()
+            for k in ks:
+                ks[k].append(t[k])
+    hog.enableTiming(False)
+    tinfo = hog.lastTimings()
+    hist_ms = statistics.mean(ks["hist_ms"])
+    alg_bytes = (CN + 2.25) * tinfo["pyramid_pixels"]
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    achieved = alg_bytes / (hist_ms * 1e-3) / 1e9
+    roofline = {"kernel": "hist_kernel<4> (fused gradient + histogram + L2-Hys, all 44 levels in one launch)",
+                "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": hist_ms,
+                "stage_ms_per_frame": {k: statistics.mean(v) for k, v in ks.items()}}
+
+    line = {"metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": CONFIG, "clocks": clocks,
+            "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "detections_per_step": nrects / max(args.steps, 1), "roofline": roofline}
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        r = cpu_reference_fps([host[0]])                      # warm-up
+        r = cpu_reference_fps([host[i % BATCH] for i in range(8)])
+        total = sum(r["times"])
+        line["cpu_baseline"] = {"value": len(r["times"]) / total, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                                "sample": "8 frames 1920x1080 of the same workload, stock cv::HOGDescriptor::detectMultiScale, "
+                                          "best frame %.1f ms" % (1e3 * min(r["times"]))}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

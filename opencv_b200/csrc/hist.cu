@@ -179,6 +179,7 @@ hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* _
     const int x = it.bx0 * kCell + c;                      // level column
     const int xl = min(max(x, 0), w - 1);                  // clamped for loads
     const bool voter = lane >= 1 && lane <= kColsPerWarp;  // owns accumulators
+    const bool tail = x >= (w & ~3);
     const bool xedge = (x <= 0) || (x >= w - 1);           // reflect-101 => dx = 0 (hog.cpp:306-313, hog.cu:646-654)
     const int nblk = min(kTileBlocks, L.nbx - it.bx0);     // blocks of this tile that exist
     const int ccl = voter ? c : 0;
@@ -206,8 +207,12 @@ hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* _
                     const float rgt = __shfl_down_sync(0xffffffffu, C[ch], 1);
                     const float ddx = xedge ? 0.f : rgt - lft;
                     const float ddy = yedge ? 0.f : D[ch] - U[ch];
-                    const float m = ddx * ddx + ddy * ddy;
-                    if (m > bm) { bm = m; bdx = ddx; bdy = ddy; }      // strict: lowest channel wins ties (hog.cu:694-712)
+                    // unfused, like the CPU's SSE2 (dx*dx)+(dy*dy): channel selection is discontinuous, an FMA here
+                    // would break exact ties such as (a,b) vs (b,a) differently from the reference
+                    const float m = __fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy));
+                    // strict >: the lowest channel wins ties (hog.cu:694-712, CPU SSE2 body hog.cpp:393-403); in the
+                    // last w%4 columns the CPU's scalar tail lets the highest channel win them (hog.cpp:455-477)
+                    if (m > bm || (tail && m == bm)) { bm = m; bdx = ddx; bdy = ddy; }
                 }
                 dx = bdx; dy = bdy;
 #pragma unroll
