@@ -1,6 +1,6 @@
 // hist.cu -- fused gradient + orientation voting + block histogram + L2-Hys kernel (sm_100a).
 //
-// Replaces, in ONE pass over each pyramid level, the reference's four kernels
+// Replaces, in ONE pass over every pyramid level of a frame, the reference's four kernels
 //   compute_gradients_8UC1/8UC4   modules/cudaobjdetect/src/cuda/hog.cu:624-821
 //   compute_hists                 hog.cu:133-279
 //   normalize_hists               hog.cu:287-386
@@ -9,40 +9,91 @@
 // (objdetect/src/hog.cpp:239-550 gradient with the fastAtan32f polynomial, :619-858 block window,
 // :1119-1248 L2-Hys) because that is the implementation the oracle can run; see DESIGN.md.
 //
-// Work decomposition (one CTA = 8 warps):
-//   * a CTA owns a tile of 240 pixel columns (30 cells -> 29 blocks) and a strip of block rows, and walks
-//     DOWN the rows: thread <-> column, so the three vertical neighbours live in registers, the two lateral
-//     ones come from warp shuffles (each warp covers 30 columns + 1 halo column each side);
-//   * the block window weight is separable, w(i,j) = A_cy[i] * A_cx[j] (Gaussian x bilinear cell weight), so
-//     votes are first accumulated VERTICALLY into per-column, per-bin partial sums in shared memory
-//     (private per thread: no atomics, fixed order, bit-reproducible), 3 live accumulators per column;
-//   * each vote pair (bin0: mag*(1-a), bin0+1: mag*a) is one 64-bit shared-memory read-modify-write: the
-//     second vote is kept in a parallel "E" plane indexed by bin0 and folded into bin0+1 at the end;
-//   * every 4 rows one accumulator is complete; a HORIZONTAL pass (warp <-> bin, lane <-> cell) contracts the
-//     240 columns with the 12-tap horizontal weights into the cell-variant sums of 29 blocks;
-//   * once both cell rows of a block row are in, 8 lanes per block do L2-Hys with shuffle reductions and write
-//     the 144-byte block histogram, coalesced across the block row.
+// The kernel is bound by instruction issue and shared-memory bandwidth, not by HBM ("hist kernel"),
+// so the design minimises instructions per pixel:
+//   * persistent grid, one CTA per SM, warps are INDEPENDENT workers pulling (level, tile, strip) items from
+//     a global queue (largest first): no block-wide barrier anywhere in the main loop;
+//   * a warp owns a tile of 120 pixel columns (15 cells -> 14 blocks); lane l in 1..30 owns 4 adjacent columns
+//     (one 16-byte load per row for 8UC4), lanes 0 and 31 carry the halo column on each side.  The warp walks
+//     DOWN the strip: vertical neighbours live in registers, lateral ones in the same thread or one shuffle away;
+//   * the block window weight is separable, w(i,j) = A_cy[i] * A_cx[j] (Gaussian x bilinear cell weight), so votes
+//     are first accumulated VERTICALLY into per-column, per-bin partial sums in shared memory (private per thread:
+//     no atomics, fixed order, bit-reproducible); each pixel feeds 3 live accumulators with one packed
+//     FFMA2 read-modify-write each: the (bin0: mag*(1-a), bin0+1: mag*a) pair is kept as a float2 indexed by bin0
+//     and the second half is folded into bin0+1 after the horizontal pass;
+//   * orientation binning is branch- and conversion-free: angle in bin units with its sign taken from
+//     sign(dx)^sign(dy), floor() by the 1.5*2^23 magic add, whose mantissa is at the same time the shared-memory
+//     row offset of the bin (no wrap needed: the 9 reachable rows are a cyclic rotation of the 9 bins);
+//   * every 4 rows one accumulator is complete; a HORIZONTAL pass (lane <-> (bin, cell)) contracts the 120 columns
+//     with the 12-tap horizontal weights into the four cell sums of 14 blocks (packed FFMA2 again);
+//   * once both cell rows of a block row are in, 4 lanes per block do L2-Hys with shuffle reductions; the 2016-byte
+//     block row leaves as coalesced 16-byte stores.
 #include "hog_internal.h"
+
+#include <cstdlib>
 
 namespace hogk {
 
 namespace {
 
-constexpr int kWarps = 8;
+constexpr int kWarps = 7;                          // independent workers per CTA (one CTA per SM)
 constexpr int kThreads = kWarps * 32;
-constexpr int kColsPerWarp = 30;
-constexpr int kCols = kWarps * kColsPerWarp;       // 240 useful columns
-constexpr int kCells = kCols / kCell;              // 30
-constexpr int kTileBlocks = kCells - 1;            // 29 blocks per tile row
-constexpr int kStripBlocks = 16;                   // block rows per strip
-constexpr int kLutCopies = 32;                     // gamma LUT replicated per bank -> conflict-free
+constexpr int kTileCells = 15;                     // 30 voting lanes x 4 columns = 120 columns
+constexpr int kTileBlocks = kTileCells - 1;        // 14 blocks per tile row
+constexpr int kStripBlocks = 8;                    // block rows per work item
+constexpr int kLutCopies = 8;                      // gamma LUT replication (bank spreading)
+constexpr int kPF = 2;                             // rows of load prefetch
 
-struct __align__(16) Smem {
-    float2 acc[3][kBins][kCols];       // 51,840 B  vertical partial sums, (D,E) pairs
-    float stgD[kTileBlocks][kHist];    //  4,176 B  horizontal results, first-vote plane
-    float stgE[kTileBlocks][kHist];    //  4,176 B  second-vote plane (belongs to bin+1)
-    float lut[256 * kLutCopies];       // 32,768 B  gamma LUT, lut[v*32 + lane]
+constexpr int kBinBytes = 4 * 32 * 8;              // one accumulator row: [j][idx] float2 = 1024 B
+constexpr int kSlotBytes = kBins * kBinBytes;      // 9216 B
+constexpr float kMagic = 12582912.f;               // 1.5 * 2^23
+
+struct __align__(16) WarpSmem {
+    float2 acc[3][kBins][4][32];                   // 27,648 B  vertical partial sums, (D,E) pairs
+    float stgD[kTileBlocks * kHist];               //  2,016 B  horizontal results, first-vote plane
+    float stgE[kTileBlocks * kHist];               //  2,016 B  second-vote plane, already shifted to its bin
 };
+struct __align__(16) Smem {
+    float4 wrow[8];                                //    128 B  vertical weights of row o of a cell row: (R, Q, P/T, -)
+    float lut[256 * kLutCopies];                   //  8,192 B  gamma LUT, lut[v*copies + lane%copies]
+    WarpSmem w[kWarps];                            // 7 x 31,680 B
+};
+
+// ---- shared-memory access to the accumulators: 32-bit shared addresses, volatile so that the batches below
+// keep their order (loads first, then stores) and ptxas is free to overlap the latencies.
+__device__ __forceinline__ float2 lds64(unsigned a)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts64(unsigned a, float2 v)
+{
+    asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a), "f"(v.x), "f"(v.y));
+}
+__device__ __forceinline__ float4 lds128(unsigned a)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128_zero(unsigned a)
+{
+    asm volatile("st.shared.v4.f32 [%0], {%1,%1,%1,%1};" ::"r"(a), "f"(0.f));
+}
+
+// packed FP32: d = a * b + c on both halves (Blackwell FFMA2)
+__device__ __forceinline__ float2 fma2(float w, float2 b, float2 c)
+{
+    unsigned long long rw, rb, rc, rd;
+    asm("mov.b64 %0, {%1,%1};" : "=l"(rw) : "f"(w));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(rw), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
 
 __device__ __forceinline__ float sqrt_approx(float x)
 {
@@ -50,236 +101,373 @@ __device__ __forceinline__ float sqrt_approx(float x)
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+template <int CN> struct RawT { typedef uint4 T; };
+template <> struct RawT<1> { typedef unsigned int T; };
 
 template <int CN>
-__device__ __forceinline__ void load_px(const uint8_t* __restrict__ row, int x, const float* __restrict__ lutl, float (&v)[3])
+__device__ __forceinline__ typename RawT<CN>::T load_raw(const uint8_t* p)
 {
-    if (CN == 4) {
-        const uchar4 p = __ldg(reinterpret_cast<const uchar4*>(row) + x);
-        v[0] = lutl[p.x * kLutCopies]; v[1] = lutl[p.y * kLutCopies]; v[2] = lutl[p.z * kLutCopies];
-    } else {
-        v[0] = lutl[__ldg(row + x) * kLutCopies];
-    }
+    return __ldg(reinterpret_cast<const typename RawT<CN>::T*>(p));
 }
 
-// vote of one pixel into one vertical accumulator: one 64-bit RMW
-__device__ __forceinline__ void vote(float2* p, float w, float g0, float g1)
+// gamma LUT (hog.cpp:258-300) of the NC channels of the 4 pixels of one thread-row
+template <int CN>
+__device__ __forceinline__ void unpack(const typename RawT<CN>::T& raw, const unsigned (&sel)[3],
+                                       const float* __restrict__ lutl, float (&v)[4][3]);
+template <>
+__device__ __forceinline__ void unpack<4>(const uint4& raw, const unsigned (&sel)[3], const float* __restrict__ lutl,
+                                          float (&v)[4][3])
 {
-    float2 v = *p;
-    v.x = fmaf(w, g0, v.x);
-    v.y = fmaf(w, g1, v.y);
-    *p = v;
-}
-
-// Horizontal contraction of one finished vertical accumulator (block row `cy` half) into the staging planes.
-// warp <-> bin, lane <-> cell k of the tile.  Also zeroes the accumulator for its next use.
-__device__ __forceinline__ void horizontal_pass(Smem& s, int slot, int cy, const BlockWeights& W, int warp, int lane)
-{
-    for (int b = warp; b < kBins; b += kWarps) {      // warp 0 also takes bin 8
-        float2 v[8];
-        if (lane < kCells) {
-            float4* p = reinterpret_cast<float4*>(&s.acc[slot][b][lane * 8]);
+    const unsigned w[4] = {raw.x, raw.y, raw.z, raw.w};
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                float4 t = p[q];
-                v[2 * q] = make_float2(t.x, t.y);
-                v[2 * q + 1] = make_float2(t.z, t.w);
-                p[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = 0; j < 4; j++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) v[j][c] = lutl[__byte_perm(w[j], 0, sel[c]) * kLutCopies];
+}
+template <>
+__device__ __forceinline__ void unpack<1>(const unsigned int& raw, const unsigned (&)[3], const float* __restrict__ lutl,
+                                          float (&v)[4][3])
+{
+#pragma unroll
+    for (int j = 0; j < 4; j++) v[j][0] = lutl[__byte_perm(raw, 0, 0x4440 + j) * kLutCopies];
+}
+
+struct Vote { unsigned off; float g0, g1; };
+
+// One pixel: centred differences, strongest channel, magnitude, orientation in bin units, interpolation weights.
+// NC = channels examined.  xm = 0 on the first / last column (reflect-101 makes dx zero there, hog.cpp:306-313).
+template <int NC>
+__device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], const float (&U)[3], const float (&D)[3],
+                                      float xm)
+{
+    float dx = (R[0] - L[0]) * xm, dy = D[0] - U[0];
+    // unfused, like the CPU's SSE2 (dx*dx)+(dy*dy): channel selection is discontinuous, an FMA here would break
+    // exact ties such as (a,b) vs (b,a) differently from the reference
+    float m = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+#pragma unroll
+    for (int c = 1; c < NC; c++) {
+        const float ddx = (R[c] - L[c]) * xm, ddy = D[c] - U[c];
+        const float mm = __fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy));
+        // strict >: the first channel in processing order wins ties (hog.cu:694-712, CPU SSE2 body hog.cpp:393-403);
+        // the caller reverses the processing order in the last w%4 columns, where the CPU's scalar tail lets the
+        // highest channel win (hog.cpp:455-477)
+        const bool p = mm > m;
+        dx = p ? ddx : dx; dy = p ? ddy : dy; m = fmaxf(m, mm);
+    }
+    const float mag = sqrt_approx(m);      // = sqrt(dx*dx + dy*dy) of the winning channel (magnitude32f)
+    // fastAtan32f (core/src/mathfuncs_core.simd.hpp:45-71), in units of one bin (20 degrees): coefficients * 9/pi
+    const float ax = fabsf(dx), ay = fabsf(dy);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float c = mn * rcp_approx(mx + 2.220446049250313e-16f);
+    const float c2 = c * c;
+    float a = ((-0.1269862277f * c2 + 0.4457000067f) * c2 - 0.9333723052f) * c2 + 2.8641811857f;
+    a *= c;
+    if (ay > ax) a = 4.5f - a;
+    // orientation modulo 180 degrees: the first-quadrant angle if dx and dy have the same sign, its negative
+    // otherwise.  q is in [-4.5, 4.5]; t = q - 0.5 is the reference's `angle*nbins/pi - 0.5` modulo 9.
+    const unsigned s = (__float_as_uint(dx) ^ __float_as_uint(dy)) & 0x80000000u;
+    const float q = __uint_as_float(__float_as_uint(a) ^ s);
+    // n = round-to-nearest-even(q) = floor(t) + 1 (a tie only moves a zero vote between two bins);
+    // the mantissa of r holds n, so r << 10 is n * 1024 bytes: the accumulator row of bin floor(t), rows being
+    // numbered n + 4 = 0..8 <-> bins 4,5,6,7,8,0,1,2,3 (hog.cpp:531-547 without the wrap)
+    const float r = q + kMagic;
+    const float nf = r - kMagic;
+    const float alpha = (q - nf) + 0.5f;
+    Vote v;
+    v.off = __float_as_uint(r) << 10;
+    v.g1 = mag * alpha;
+    v.g0 = mag - v.g1;
+    return v;
+}
+
+// Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row) into the staging planes;
+// also zeroes the accumulator for its next use.  lane <-> (accumulator row, cell): 2 rows x 15 cells per pass.
+__device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws, int cy, const BlockWeights& W, int lane)
+{
+    const int cell = lane & 15, half = lane >> 4;
+    float a0[8], a18[8], a08[4], a1[4];
+#pragma unroll
+    for (int p = 0; p < 8; p++) { a0[p] = W.a0[p]; a18[p] = W.a1[8 + p]; }
+#pragma unroll
+    for (int p = 0; p < 4; p++) { a08[p] = W.a0[8 + p]; a1[p] = W.a1[4 + p]; }
+#pragma unroll 1
+    for (int it = 0; it < 5; it++) {
+        const int row = it * 2 + half;
+        const bool act = cell < kTileCells && row < kBins;
+        float2 v[8];
+        if (act) {
+            const unsigned base = slot_addr + row * kBinBytes + cell * 16;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float4 t = lds128(base + j * 256);          // columns j and 4+j of the cell
+                v[j] = make_float2(t.x, t.y);
+                v[4 + j] = make_float2(t.z, t.w);
             }
+#pragma unroll
+            for (int j = 0; j < 4; j++) sts128_zero(base + j * 256);
         } else {
 #pragma unroll
-            for (int q = 0; q < 8; q++) v[q] = make_float2(0.f, 0.f);
+            for (int p = 0; p < 8; p++) v[p] = make_float2(0.f, 0.f);
         }
         float2 s00 = make_float2(0.f, 0.f), s11 = s00, s01 = s00, s10 = s00;
 #pragma unroll
         for (int p = 0; p < 8; p++) {
-            s00.x = fmaf(W.a0[p], v[p].x, s00.x);     s00.y = fmaf(W.a0[p], v[p].y, s00.y);      // cell k = cx0 of block k
-            s11.x = fmaf(W.a1[8 + p], v[p].x, s11.x); s11.y = fmaf(W.a1[8 + p], v[p].y, s11.y);  // cell k = cx1 of block k-1
-            if (p < 4) { s01.x = fmaf(W.a0[8 + p], v[p].x, s01.x); s01.y = fmaf(W.a0[8 + p], v[p].y, s01.y); }  // -> cx0 of block k-1
-            else       { s10.x = fmaf(W.a1[p], v[p].x, s10.x);     s10.y = fmaf(W.a1[p], v[p].y, s10.y); }      // -> cx1 of block k
+            s00 = fma2(a0[p], v[p], s00);                          // cell k = cx0 of block k
+            s11 = fma2(a18[p], v[p], s11);                         // cell k = cx1 of block k-1
+            if (p < 4) s01 = fma2(a08[p], v[p], s01);              // -> cx0 of block k-1
+            else       s10 = fma2(a1[p - 4], v[p], s10);           // -> cx1 of block k
         }
-        // block k, cx=0  = own s00 + s01 of cell k+1 ; block k-1, cx=1 = own s11 + s10 of cell k-1
+        // block k, cx=0 = own s00 + s01 of cell k+1 ; block k-1, cx=1 = own s11 + s10 of cell k-1
         const float ax = s00.x + __shfl_down_sync(0xffffffffu, s01.x, 1);
         const float ay = s00.y + __shfl_down_sync(0xffffffffu, s01.y, 1);
         const float bx = s11.x + __shfl_up_sync(0xffffffffu, s10.x, 1);
         const float by = s11.y + __shfl_up_sync(0xffffffffu, s10.y, 1);
-        if (lane < kTileBlocks) { s.stgD[lane][(0 * 2 + cy) * kBins + b] = ax; s.stgE[lane][(0 * 2 + cy) * kBins + b] = ay; }
-        if (lane >= 1 && lane < kCells) { s.stgD[lane - 1][(1 * 2 + cy) * kBins + b] = bx; s.stgE[lane - 1][(1 * 2 + cy) * kBins + b] = by; }
+        const int tb = row + 4 >= kBins ? row + 4 - kBins : row + 4;     // bin of this accumulator row
+        const int te = tb + 1 >= kBins ? 0 : tb + 1;                     // the second votes belong to the next bin
+        if (act && cell < kTileBlocks) {
+            ws.stgD[cell * kHist + (0 * 2 + cy) * kBins + tb] = ax;
+            ws.stgE[cell * kHist + (0 * 2 + cy) * kBins + te] = ay;
+        }
+        if (act && cell >= 1) {
+            ws.stgD[(cell - 1) * kHist + (1 * 2 + cy) * kBins + tb] = bx;
+            ws.stgE[(cell - 1) * kHist + (1 * 2 + cy) * kBins + te] = by;
+        }
     }
 }
 
-// L2-Hys (hog.cpp:1119-1248 / hog.cu:333-349) of the staged block row and store; 8 lanes per block.
-__device__ __forceinline__ void normalize_store(const Smem& s, int tid, int nblk, float thr, float* __restrict__ out_row)
+__device__ __forceinline__ void zero_slot(unsigned slot_addr, int lane)
 {
-    const int blk = tid >> 3, l = tid & 7;
-    float v[5];
-    float ss = 0.f;
 #pragma unroll
-    for (int j = 0; j < 5; j++) {
-        const int idx = l + 8 * j;
-        v[j] = 0.f;
-        if (idx < kHist && blk < nblk) {
-            const int b = idx % kBins;
-            const int eidx = b ? idx - 1 : idx + kBins - 1;     // second votes of bin b-1 land in bin b
-            v[j] = s.stgD[blk][idx] + s.stgE[blk][eidx];
+    for (int i = 0; i < kSlotBytes / (32 * 16); i++) sts128_zero(slot_addr + (i * 32 + lane) * 16);
+}
+
+// L2-Hys (hog.cpp:1119-1248 / hog.cu:333-349) of the staged block row and coalesced store; 4 lanes per block,
+// one cell (9 bins) per lane.
+__device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk, float thr, float* __restrict__ out_row)
+{
+#pragma unroll 1
+    for (int g = 0; g < 2; g++) {
+        // (block, cell) -> 9 consecutive staging floats; the two lanes past block 13 recompute block 13 (no store)
+        const bool live = g * 8 + (lane >> 2) < kTileBlocks;
+        const int idx = live ? (g * 32 + lane) * kBins : (kTileBlocks * 4 - 4 + (lane & 3)) * kBins;
+        float v[kBins];
+        float ss = 0.f;
+#pragma unroll
+        for (int b = 0; b < kBins; b++) {
+            v[b] = ws.stgD[idx + b] + ws.stgE[idx + b];
+            ss = fmaf(v[b], v[b], ss);
         }
-        ss = fmaf(v[j], v[j], ss);
-    }
-    ss += __shfl_xor_sync(0xffffffffu, ss, 1);
-    ss += __shfl_xor_sync(0xffffffffu, ss, 2);
-    ss += __shfl_xor_sync(0xffffffffu, ss, 4);
-    const float sc1 = 1.f / (sqrtf(ss) + kHist * 0.1f);
-    float s2 = 0.f;
+        ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+        ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+        const float sc1 = 1.f / (sqrtf(ss) + kHist * 0.1f);
+        float s2 = 0.f;
 #pragma unroll
-    for (int j = 0; j < 5; j++) {
-        v[j] = fminf(v[j] * sc1, thr);
-        s2 = fmaf(v[j], v[j], s2);
-    }
-    s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
-    s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
-    s2 += __shfl_xor_sync(0xffffffffu, s2, 4);
-    const float sc2 = 1.f / (sqrtf(s2) + 1e-3f);
-    if (blk < nblk) {
-#pragma unroll
-        for (int j = 0; j < 5; j++) {
-            const int idx = l + 8 * j;
-            if (idx < kHist) out_row[blk * kHist + idx] = v[j] * sc2;
+        for (int b = 0; b < kBins; b++) {
+            v[b] = fminf(v[b] * sc1, thr);
+            s2 = fmaf(v[b], v[b], s2);
         }
+        s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
+        const float sc2 = 1.f / (sqrtf(s2) + 1e-3f);
+        __syncwarp();       // every lane has read its inputs before any lane overwrites the plane
+        if (live) {
+#pragma unroll
+            for (int b = 0; b < kBins; b++) ws.stgD[idx + b] = v[b] * sc2;
+        }
+    }
+    __syncwarp();
+    const float4* src = reinterpret_cast<const float4*>(ws.stgD);
+    float4* dst = reinterpret_cast<float4*>(out_row);
+    for (int i = lane; i < nblk * (kHist / 4); i += 32) dst[i] = src[i];
+}
+
+template <int CN>
+__device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistItem it, const LevelDesc& L,
+                                             const uint8_t* __restrict__ base, int base_pitch, const BlockWeights& W,
+                                             float l2hys, float* __restrict__ hist, int lane)
+{
+    constexpr int NC = CN == 4 ? 3 : 1;
+    constexpr int kChunk = 4 * CN;                          // bytes of 4 pixels
+    const int w = L.w, h = L.h, pitch = L.img ? L.pitch : base_pitch;
+    const uint8_t* __restrict__ img = L.img ? L.img : base;  // level 0 aliases the frame
+    const int xt = it.bx0 * kCell - 4 + 4 * lane;           // first of this lane's 4 columns (lane 0 / 31: halo)
+    const int chunk = min(max(xt >> 2, 0), (w - 1) >> 2);   // clamped: out-of-range columns never reach an output
+    const uint8_t* __restrict__ colp = img + (size_t)chunk * kChunk;
+    float xm[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) xm[j] = (xt + j <= 0 || xt + j >= w - 1) ? 0.f : 1.f;
+    // channel processing order: B,G,R -- reversed in the columns of the CPU's scalar tail (x >= w & ~3)
+    const bool tail = xt >= (w & ~3);
+    const unsigned sel[3] = {0x4440u + (tail ? 2u : 0u), 0x4441u, 0x4440u + (tail ? 0u : 2u)};
+    const bool swap_l = tail != (xt - 4 >= (w & ~3)), swap_r = tail != (xt + 4 >= (w & ~3));
+    const float* __restrict__ lutl = s.lut + (lane % kLutCopies);
+    const int nblk = min(kTileBlocks, L.nbx - it.bx0);      // blocks of this tile that exist
+
+    // accumulator slots: roles P (block row above, cell row 0), Q (above, cell row 1), R (this, cell row 0);
+    // lane l votes into element (l-1)&31 of every [bin][j] row, rows of one slot are 1024 B apart
+    const unsigned acc0 = (unsigned)__cvta_generic_to_shared(&ws.acc[0][0][0][0]);
+    const unsigned lane_off = ((lane - 1) & 31) * 8 + 4 * kBinBytes;   // + 4 rows: row index = n + 4
+    unsigned sp = acc0, sq = acc0 + kSlotBytes, sr = acc0 + 2 * kSlotBytes;
+    zero_slot(sr, lane);                                    // P and Q are cleared during the first cell row
+    __syncwarp();
+
+    int y = it.by0 * kCell;
+    float U[4][3], C[4][3], D[4][3];
+    typename RawT<CN>::T pf[kPF];
+    {
+        const int yu = y == 0 ? 1 : y - 1;                  // reflect-101: dy = 0 on the first row
+        unpack<CN>(load_raw<CN>(colp + (size_t)yu * pitch), sel, lutl, U);
+        unpack<CN>(load_raw<CN>(colp + (size_t)y * pitch), sel, lutl, C);
+#pragma unroll
+        for (int k = 0; k < kPF; k++) {
+            const int yy = y + 1 + k;
+            pf[k] = load_raw<CN>(colp + (size_t)(yy >= h ? h - 2 : yy) * pitch);
+        }
+    }
+
+#pragma unroll 1
+    for (int cr = 0; cr <= it.nby; cr++) {
+#pragma unroll 1
+        for (int hf = 0; hf < 2; hf++) {
+            float wr[4], wq[4], wp[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const float4 t = s.wrow[hf * 4 + k];
+                wr[k] = t.x; wq[k] = t.y; wp[k] = t.z;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++, y++) {
+                // row y+1 (reflect-101 at the bottom: dy = 0 on the last row), and the prefetch kPF rows ahead
+                unpack<CN>(pf[k % kPF], sel, lutl, D);
+                {
+                    const int yy = y + 1 + kPF;
+                    pf[k % kPF] = load_raw<CN>(colp + (size_t)(yy >= h ? h - 2 : yy) * pitch);
+                }
+                float lf[3], rt[3];
+#pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    lf[c] = __shfl_up_sync(0xffffffffu, C[3][c], 1);
+                    rt[c] = __shfl_down_sync(0xffffffffu, C[0][c], 1);
+                }
+                if (NC == 3) {      // a neighbour on the other side of the tail boundary stores its channels reversed
+                    const float l0 = lf[0], r0 = rt[0];
+                    lf[0] = swap_l ? lf[2] : l0; lf[2] = swap_l ? l0 : lf[2];
+                    rt[0] = swap_r ? rt[2] : r0; rt[2] = swap_r ? r0 : rt[2];
+                }
+                Vote v[4];
+                v[0] = pixel<NC>(lf, C[1], U[0], D[0], xm[0]);
+                v[1] = pixel<NC>(C[0], C[2], U[1], D[1], xm[1]);
+                v[2] = pixel<NC>(C[1], C[3], U[2], D[2], xm[2]);
+                v[3] = pixel<NC>(C[2], rt, U[3], D[3], xm[3]);
+                // ---- vertical accumulation: 12 private read-modify-writes, loads first
+                float2 ar[4], aq[4], ap[4];
+                unsigned ad[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    ad[j] = v[j].off + lane_off + j * 256;
+                    ar[j] = lds64(ad[j] + sr); aq[j] = lds64(ad[j] + sq); ap[j] = lds64(ad[j] + sp);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float2 g = make_float2(v[j].g0, v[j].g1);
+                    ar[j] = fma2(wr[k], g, ar[j]); aq[j] = fma2(wq[k], g, aq[j]); ap[j] = fma2(wp[k], g, ap[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; j++) { sts64(ad[j] + sr, ar[j]); sts64(ad[j] + sq, aq[j]); sts64(ad[j] + sp, ap[j]); }
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+#pragma unroll
+                    for (int c = 0; c < NC; c++) { U[j][c] = C[j][c]; C[j][c] = D[j][c]; }
+            }
+            __syncwarp();
+            const unsigned done = hf ? sq : sp;             // P is complete after 4 rows, Q after 8
+            if (cr == 0) zero_slot(done, lane);
+            else horizontal_pass(done, ws, hf, W, lane);
+            __syncwarp();
+            if (hf && cr > 0) {
+                const int by = it.by0 + cr - 1;
+                normalize_store(ws, lane, nblk, l2hys, hist + L.hist_off + ((long long)by * L.nbx + it.bx0) * kHist);
+                __syncwarp();
+            }
+        }
+        // rotate roles: R -> P, T (in P's slot) -> Q, Q's slot (just consumed and zeroed) -> R
+        const unsigned t = sp; sp = sr; sr = sq; sq = t;
     }
 }
 
 template <int CN>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 1)
 hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* __restrict__ levels,
-            const HistItem* __restrict__ items, int gamma, const BlockWeights W, float l2hys,
-            float* __restrict__ hist)
+            const HistItem* __restrict__ items, int nitems, unsigned int* __restrict__ queue, int gamma,
+            const BlockWeights W, float l2hys, float* __restrict__ hist)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-    const HistItem it = items[blockIdx.x];
-    const LevelDesc& L = levels[it.level];
-    const int w = L.w, h = L.h, pitch = L.img ? L.pitch : base_pitch;
-    const uint8_t* __restrict__ img = L.img ? L.img : base;   // level 0 aliases the frame
-
-    // gamma LUT (hog.cpp:258-300): sqrt(v) or v, replicated so that lane l only touches bank l
+    // gamma LUT (hog.cpp:258-300): sqrt(v) or v, replicated so that lanes spread over the banks
     for (int i = tid; i < 256 * kLutCopies; i += kThreads) {
         const float v = (float)(i / kLutCopies);
         s.lut[i] = gamma ? sqrtf(v) : v;
     }
-    {   // zero the three vertical accumulators once; afterwards the horizontal pass re-zeroes what it consumes
-        float4* p = reinterpret_cast<float4*>(&s.acc[0][0][0]);
-        for (int i = tid; i < (int)(sizeof(s.acc) / 16); i += kThreads) p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tid < 8) {
+        // row o of a cell row feeds R: block row cr, cell row 0, i = o;  Q: block row cr-1, cell row 1, i = 8+o;
+        // P (o<4): block row cr-1, cell row 0, i = 8+o  or  T (o>=4): block row cr, cell row 1, i = o
+        const int o = tid;
+        s.wrow[o] = make_float4(W.a0[o], W.a1[8 + o], o < 4 ? W.a0[8 + o] : W.a1[o], 0.f);
     }
     __syncthreads();
 
-    const float* lutl = s.lut + lane;
-    const int c = warp * kColsPerWarp + lane - 1;          // tile column of this thread, -1 and 240 are halo
-    const int x = it.bx0 * kCell + c;                      // level column
-    const int xl = min(max(x, 0), w - 1);                  // clamped for loads
-    const bool voter = lane >= 1 && lane <= kColsPerWarp;  // owns accumulators
-    const bool tail = x >= (w & ~3);
-    const bool xedge = (x <= 0) || (x >= w - 1);           // reflect-101 => dx = 0 (hog.cpp:306-313, hog.cu:646-654)
-    const int nblk = min(kTileBlocks, L.nbx - it.bx0);     // blocks of this tile that exist
-    const int ccl = voter ? c : 0;
-
-    int y = it.by0 * kCell;
-    float U[3], C[3], D[3];
-    load_px<CN>(img + (size_t)max(y - 1, 0) * pitch, xl, lutl, U);
-    load_px<CN>(img + (size_t)min(y, h - 1) * pitch, xl, lutl, C);
-
-    int sp = 0, sq = 1, sr = 2;     // accumulator slots of roles P (block row above, cell row 0), Q (above, cell row 1), R (this, cell row 0)
-
-    for (int cr = 0; cr <= it.nby; cr++) {
-        const bool first = cr == 0, last = cr == it.nby;
-#pragma unroll
-        for (int o = 0; o < 8; o++, y++) {
-            load_px<CN>(img + (size_t)min(y + 1, h - 1) * pitch, xl, lutl, D);
-            // ---- gradient: centred differences on gamma-corrected values, strongest channel wins
-            float dx, dy;
-            {
-                const bool yedge = (y == 0) || (y >= h - 1);
-                float bdx = 0.f, bdy = 0.f, bm = -1.f;
-#pragma unroll
-                for (int ch = 0; ch < (CN == 4 ? 3 : 1); ch++) {
-                    const float lft = __shfl_up_sync(0xffffffffu, C[ch], 1);
-                    const float rgt = __shfl_down_sync(0xffffffffu, C[ch], 1);
-                    const float ddx = xedge ? 0.f : rgt - lft;
-                    const float ddy = yedge ? 0.f : D[ch] - U[ch];
-                    // unfused, like the CPU's SSE2 (dx*dx)+(dy*dy): channel selection is discontinuous, an FMA here
-                    // would break exact ties such as (a,b) vs (b,a) differently from the reference
-                    const float m = __fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy));
-                    // strict >: the lowest channel wins ties (hog.cu:694-712, CPU SSE2 body hog.cpp:393-403); in the
-                    // last w%4 columns the CPU's scalar tail lets the highest channel win them (hog.cpp:455-477)
-                    if (m > bm || (tail && m == bm)) { bm = m; bdx = ddx; bdy = ddy; }
-                }
-                dx = bdx; dy = bdy;
-#pragma unroll
-                for (int ch = 0; ch < (CN == 4 ? 3 : 1); ch++) { U[ch] = C[ch]; C[ch] = D[ch]; }
-            }
-            // ---- magnitude and orientation (cartToPolar: mathfuncs_core.simd.hpp:45-71, 194-225)
-            const float mag = sqrt_approx(fmaf(dx, dx, dy * dy));
-            const float ax = fabsf(dx), ay = fabsf(dy);
-            const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
-            const float cc = __fdividef(mn, mx + 2.220446049250313e-16f);
-            const float c2 = cc * cc;
-            float a = (((-0.04432655554792128f * 57.29577951308232f * c2 + 0.1555786518463281f * 57.29577951308232f) * c2
-                        - 0.3258083974640975f * 57.29577951308232f) * c2 + 0.9997878412794807f * 57.29577951308232f) * cc;
-            if (ay > ax) a = 90.f - a;
-            if (dx < 0.f) a = 180.f - a;
-            if (dy < 0.f) a = 360.f - a;
-            // ---- bin interpolation (hog.cpp:531-547): 9 bins over 180 degrees
-            float t = (a * 0.017453292519943295f) * 2.864788975654116f - 0.5f;
-            const float fl = floorf(t);
-            const float alpha = t - fl;
-            int bin0 = (int)fl;
-            bin0 = bin0 < 0 ? bin0 + kBins : (bin0 >= kBins ? bin0 - kBins : bin0);
-            const float g1 = mag * alpha, g0 = mag * (1.f - alpha);
-            // ---- vertical accumulation: this row feeds 3 of the live accumulators
-            if (voter) {
-                float2* base = &s.acc[0][bin0][ccl];
-                constexpr int kSlot = kBins * kCols;
-                if (!last) vote(base + sr * kSlot, W.a0[o], g0, g1);                    // R: block row cr,   cell row 0, i = o
-                if (!first) vote(base + sq * kSlot, W.a1[8 + o], g0, g1);               // Q: block row cr-1, cell row 1, i = 8+o
-                if (o < 4) { if (!first) vote(base + sp * kSlot, W.a0[8 + o], g0, g1); }  // P: block row cr-1, cell row 0, i = 8+o
-                else       { if (!last) vote(base + sp * kSlot, W.a1[o], g0, g1); }       // T: block row cr,   cell row 1, i = o
-            }
-            if (o == 3 && !first) {
-                __syncthreads();
-                horizontal_pass(s, sp, 0, W, warp, lane);
-                __syncthreads();
-            }
-        }
-        if (!first) {
-            __syncthreads();
-            horizontal_pass(s, sq, 1, W, warp, lane);
-            __syncthreads();
-            const int by = it.by0 + cr - 1;
-            normalize_store(s, tid, nblk, l2hys, hist + L.hist_off + ((long long)by * L.nbx + it.bx0) * kHist);
-        }
-        // rotate roles: R -> P, T (in P's slot) -> Q, Q's slot (just consumed and zeroed) -> R
-        const int t = sp; sp = sr; sr = sq; sq = t;
+    WarpSmem& ws = s.w[warp];
+    for (;;) {
+        int idx = 0;
+        if (lane == 0) idx = (int)atomicAdd(&queue[0], 1u);
+        idx = __shfl_sync(0xffffffffu, idx, 0);
+        if (idx >= nitems) break;
+        const HistItem it = items[idx];
+        process_item<CN>(s, ws, it, levels[it.level], base, base_pitch, W, l2hys, hist, lane);
+    }
+    // the last worker to run dry re-arms the queue for the next launch on this stream
+    if (lane == 0) {
+        const unsigned d = atomicAdd(&queue[1], 1u);
+        if (d == gridDim.x * kWarps - 1) { queue[0] = 0u; queue[1] = 0u; }
     }
 }
 
 }  // namespace
 
 int hist_tile_blocks_x() { return kTileBlocks; }
-int hist_strip_blocks_y() { return kStripBlocks; }
+int hist_strip_blocks_y()
+{
+    static const int v = [] {
+        const char* e = getenv("HOGB200_STRIP");       // tuning knob: block rows per work item
+        const int n = e ? atoi(e) : 0;
+        return n > 0 && n <= 512 ? n : kStripBlocks;
+    }();
+    return v;
+}
 
 void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels, const HistItem* d_items,
-                 int nitems, int cn, int gamma, const BlockWeights& bw, float l2hys, float* d_hist,
-                 cudaStream_t st)
+                 int nitems, unsigned int* d_queue, int num_sms, int cn, int gamma, const BlockWeights& bw, float l2hys,
+                 float* d_hist, cudaStream_t st)
 {
     if (nitems <= 0) return;
+    const int grid = max(1, min(num_sms, (nitems + kWarps - 1) / kWarps));
     // per-device attribute (cheap host call); the handle may live on any device
-    cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    cudaFuncSetAttribute(hist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-    if (cn == 4)
-        hist_kernel<4><<<nitems, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, gamma, bw, l2hys, d_hist);
-    else
-        hist_kernel<1><<<nitems, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, gamma, bw, l2hys, d_hist);
+    if (cn == 4) {
+        cudaFuncSetAttribute(hist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        hist_kernel<4><<<grid, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
+    } else {
+        cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        hist_kernel<1><<<grid, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
+    }
 }
 
 }  // namespace hogk

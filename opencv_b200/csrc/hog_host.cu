@@ -106,6 +106,8 @@ struct hogb200 {
     cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
     // workspace
     DevBuf<uint8_t> d_frame[2]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
+    DevBuf<unsigned int> d_queue;   // work-queue counters of the fused histogram kernel (self re-arming)
+    int num_sms = 148;
     DevBuf<unsigned char> d_cand;   // [16-byte header: counter][Candidate * cap]
     size_t cand_cap = 0;
     PinBuf<unsigned char> h_cand;
@@ -263,6 +265,10 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
         P.lv.push_back(L); descs.push_back(D);
     }
     (void)sbx; (void)sby;
+    // the histogram kernel's workers pull items from a queue: longest first, so that the tail is made of short ones
+    std::stable_sort(hitems.begin(), hitems.end(), [](const HistItem& a, const HistItem& b) {
+        return a.nby > b.nby;       // a partial tile costs a warp as much as a full one
+    });
     P.pyr_bytes = pyr;
     CK(h->d_pyr.reserve(pyr + 256));
     for (size_t i = 0; i < descs.size(); i++)
@@ -306,7 +312,12 @@ int stage_frame(hogb200* h, const hogb200_image* img, int buf, cudaStream_t st, 
 {
     const int cn = img->channels;
     const size_t row = (size_t)img->width * cn;
-    if (img->on_device && ((uintptr_t)img->data % 4 == 0) && (img->pitch % 4 == 0 || cn == 1) && img->pitch < (1u << 30)) {
+    // the kernels read rows in 4-pixel vectors: 16-byte aligned rows for 8UC4, 4-byte for 8UC1, and (so that
+    // the last vector of the last row stays inside the caller's buffer) a width that is a multiple of 4
+    // unless the pitch leaves room; anything else goes through the staging copy below
+    const size_t al = cn == 4 ? 16 : 4;
+    if (img->on_device && ((uintptr_t)img->data % al == 0) && (img->pitch % al == 0) && img->pitch < (1u << 30) &&
+        (img->width % 4 == 0 || img->pitch >= align_up(row, al))) {
         out.dev = (const uint8_t*)img->data; out.pitch = (int)img->pitch;
         return HOGB200_OK;
     }
@@ -341,8 +352,8 @@ int queue_frame(hogb200* h, Plan& P, FrameRef f, int ndet, const int* slots, flo
     }
     if (h->timing) cudaEventRecord(h->ev[2], st);
     if (P.n_hist) {
-        launch_hist(f.dev, f.pitch, P.d_levels.p, P.d_hitems.p, P.n_hist, P.cn, h->gamma, make_weights(h->win_sigma),
-                    (float)h->l2hys, h->d_hist.p, st);
+        launch_hist(f.dev, f.pitch, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
+                    make_weights(h->win_sigma), (float)h->l2hys, h->d_hist.p, st);
         (*launches)++;
     }
     if (h->timing) cudaEventRecord(h->ev[3], st);
@@ -549,6 +560,9 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->fr_done[i], cudaEventDisableTiming);
     }
     for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&h->ev[i]);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = h->d_queue.reserve(4);
+    if (e == cudaSuccess) e = cudaMemset(h->d_queue.p, 0, 4 * sizeof(unsigned int));
     if (e != cudaSuccess) {
         cudaGetLastError();
         hogb200_destroy(h);
@@ -566,7 +580,7 @@ void hogb200_destroy(hogb200_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (int i = 0; i < kMaxDet; i++) h->d_det[i].release();
     h->d_frame[0].release(); h->d_frame[1].release(); h->d_pyr.release(); h->d_hist.release();
-    h->d_scores.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
+    h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
     for (Plan* P : {&h->plan, &h->plan1}) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();

@@ -35,7 +35,7 @@ struct LevelDesc {
 // c0/c1 = 11-bit fixed-point weights (resize.cpp:3647-3655)
 struct ResizeCoef { int ofs; short c0, c1; };
 
-// work item of the fused gradient+histogram kernel: a strip of block rows x a tile of block columns
+// work item of the fused gradient+histogram kernel (one warp): a strip of block rows x a tile of block columns
 struct HistItem { short level; short bx0; short by0; short nby; };   // nby = block rows in this strip
 // work item of the SVM kernel: a tile of windows of one level
 struct SvmItem { short level; short wx0; short wy0; short pad; };
@@ -55,9 +55,12 @@ void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);
 
 // base/base_pitch: the frame itself, used for levels whose LevelDesc::img is null (level 0 aliases the frame)
+// d_queue: two zero-initialised counters in device memory (work queue head, finished workers); the kernel
+// re-arms them itself, so consecutive launches on one stream need no host reset.  Rows of the level images
+// must be 16-byte aligned for cn == 4 (4-byte for cn == 1).
 void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels, const HistItem* d_items,
-                 int nitems, int cn, int gamma, const BlockWeights& bw, float l2hys, float* d_hist,
-                 cudaStream_t st);
+                 int nitems, unsigned int* d_queue, int num_sms, int cn, int gamma, const BlockWeights& bw,
+                 float l2hys, float* d_hist, cudaStream_t st);
 
 struct SvmParams {
     int win_bx, win_by;        // window size in blocks (7 x 15)
@@ -81,7 +84,7 @@ int svm_tile_wy();
 void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_hist, int win_bx, int win_by,
                     int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);
 
-int hist_tile_blocks_x();   // blocks per tile in x (29)
+int hist_tile_blocks_x();   // blocks per tile in x (14)
 int hist_strip_blocks_y();  // block rows per strip
 
 }  // namespace hogk
