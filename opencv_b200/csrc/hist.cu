@@ -42,7 +42,7 @@ constexpr int kTileCells = 15;                     // 30 voting lanes x 4 column
 constexpr int kTileBlocks = kTileCells - 1;        // 14 blocks per tile row
 constexpr int kStripBlocks = 8;                    // block rows per work item
 constexpr int kLutCopies = 8;                      // gamma LUT replication (bank spreading)
-constexpr int kPF = 2;                             // rows of load prefetch
+constexpr int kPF = 4;                             // rows of load prefetch
 
 constexpr int kBinBytes = 4 * 32 * 8;              // one accumulator row: [j][idx] float2 = 1024 B
 constexpr int kSlotBytes = kBins * kBinBytes;      // 9216 B
@@ -197,24 +197,22 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
     for (int p = 0; p < 8; p++) { a0[p] = W.a0[p]; a18[p] = W.a1[8 + p]; }
 #pragma unroll
     for (int p = 0; p < 4; p++) { a08[p] = W.a0[8 + p]; a1[p] = W.a1[4 + p]; }
-#pragma unroll 1
+#pragma unroll
     for (int it = 0; it < 5; it++) {
         const int row = it * 2 + half;
-        const bool act = cell < kTileCells && row < kBins;
+        const bool act = row < kBins;        // the 10th row slot re-reads row 8 and stores nothing
+        // lanes of cell 15 read (and clear) the two halo elements: whatever they hold only reaches sums nobody stores
+        const unsigned base = slot_addr + min(row, kBins - 1) * kBinBytes + cell * 16;
         float2 v[8];
-        if (act) {
-            const unsigned base = slot_addr + row * kBinBytes + cell * 16;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const float4 t = lds128(base + j * 256);          // columns j and 4+j of the cell
-                v[j] = make_float2(t.x, t.y);
-                v[4 + j] = make_float2(t.z, t.w);
-            }
+        for (int j = 0; j < 4; j++) {
+            const float4 t = lds128(base + j * 256);              // columns j and 4+j of the cell
+            v[j] = make_float2(t.x, t.y);
+            v[4 + j] = make_float2(t.z, t.w);
+        }
+        if (act) {
 #pragma unroll
             for (int j = 0; j < 4; j++) sts128_zero(base + j * 256);
-        } else {
-#pragma unroll
-            for (int p = 0; p < 8; p++) v[p] = make_float2(0.f, 0.f);
         }
         float2 s00 = make_float2(0.f, 0.f), s11 = s00, s01 = s00, s10 = s00;
 #pragma unroll
@@ -235,7 +233,7 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
             ws.stgD[cell * kHist + (0 * 2 + cy) * kBins + tb] = ax;
             ws.stgE[cell * kHist + (0 * 2 + cy) * kBins + te] = ay;
         }
-        if (act && cell >= 1) {
+        if (act && cell >= 1 && cell < kTileCells) {
             ws.stgD[(cell - 1) * kHist + (1 * 2 + cy) * kBins + tb] = bx;
             ws.stgE[(cell - 1) * kHist + (1 * 2 + cy) * kBins + te] = by;
         }
@@ -266,7 +264,7 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         }
         ss += __shfl_xor_sync(0xffffffffu, ss, 1);
         ss += __shfl_xor_sync(0xffffffffu, ss, 2);
-        const float sc1 = 1.f / (sqrtf(ss) + kHist * 0.1f);
+        const float sc1 = rcp_approx(sqrt_approx(ss) + kHist * 0.1f);
         float s2 = 0.f;
 #pragma unroll
         for (int b = 0; b < kBins; b++) {
@@ -275,7 +273,7 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         }
         s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
         s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
-        const float sc2 = 1.f / (sqrtf(s2) + 1e-3f);
+        const float sc2 = rcp_approx(sqrt_approx(s2) + 1e-3f);
         __syncwarp();       // every lane has read its inputs before any lane overwrites the plane
         if (live) {
 #pragma unroll
@@ -426,13 +424,19 @@ hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* _
     __syncthreads();
 
     WarpSmem& ws = s.w[warp];
-    for (;;) {
-        int idx = 0;
-        if (lane == 0) idx = (int)atomicAdd(&queue[0], 1u);
-        idx = __shfl_sync(0xffffffffu, idx, 0);
-        if (idx >= nitems) break;
-        const HistItem it = items[idx];
+    // work queue, one item ahead: the next index and descriptor are in flight while the current item is processed
+    auto fetch = [&]() {
+        int i = 0;
+        if (lane == 0) i = (int)atomicAdd(&queue[0], 1u);
+        return __shfl_sync(0xffffffffu, i, 0);
+    };
+    int idx = fetch();
+    HistItem it = items[min(idx, nitems - 1)];
+    while (idx < nitems) {
+        const int nidx = fetch();
+        const HistItem nit = items[min(nidx, nitems - 1)];
         process_item<CN>(s, ws, it, levels[it.level], base, base_pitch, W, l2hys, hist, lane);
+        idx = nidx; it = nit;
     }
     // the last worker to run dry re-arms the queue for the next launch on this stream
     if (lane == 0) {
