@@ -175,6 +175,7 @@ void resize_table(int src, int dst, bool is_x, std::vector<ResizeCoef>& out)
 {
     const double inv_scale = (double)dst / src;     // resize.cpp:3730-3731
     const double scale = 1. / inv_scale;            // :3481
+    auto clip = [](int x, int a, int b) { return x >= a ? (x < b ? x : b - 1) : a; };   // resize.cpp:1773-1776
     for (int d = 0; d < dst; d++) {
         float f = (float)((d + 0.5) * scale - 0.5);
         int s = cvFloorF(f);
@@ -183,10 +184,11 @@ void resize_table(int src, int dst, bool is_x, std::vector<ResizeCoef>& out)
             if (s < 0) { f = 0; s = 0; }
             if (s >= src - 1) { f = 0; s = src - 1; }   // :3631-3636 (xmax handling: second tap has weight 0)
         }
+        const unsigned c0 = (unsigned)(unsigned short)(short)lrintf((1.f - f) * 2048);
+        const unsigned c1 = (unsigned)(unsigned short)(short)lrintf(f * 2048);
         ResizeCoef c;
-        c.ofs = s;
-        c.c0 = (short)lrintf((1.f - f) * 2048);
-        c.c1 = (short)lrintf(f * 2048);
+        if (is_x) { c.s0 = s; c.s1 = std::min(s + 1, src - 1); c.c0 = c0 | (c1 << 16); c.c1 = 0; }
+        else      { c.s0 = clip(s, 0, src); c.s1 = clip(s + 1, 0, src); c.c0 = c0 << 16; c.c1 = c1 << 16; }   // rows: :1821-1825
         out.push_back(c);
     }
 }
@@ -248,8 +250,8 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
             L.img_off = pyr; pyr += align_up((size_t)L.pitch * L.h, 256);
             D.xtab_off = (int)xtab.size(); D.ytab_off = (int)ytab.size();
             if (L.mode == 1) { resize_table(W, L.w, true, xtab); resize_table(H, L.h, false, ytab); }
-            const int tw = cn == 4 ? 32 : 128;
-            for (int y = 0; y < L.h; y += 8)
+            const int tw = resize_tile_w(cn), th = resize_tile_h(cn);
+            for (int y = 0; y < L.h; y += th)
                 for (int x = 0; x < L.w; x += tw) ritems.push_back(ResizeItem{(short)i, (short)x, (short)y, 0});
         }
         D.w = L.w; D.h = L.h; D.nbx = L.nbx; D.nby = L.nby; D.nwx = L.nwx; D.nwy = L.nwy;
@@ -918,8 +920,8 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
     D.mode = is_exact_half(W, H, dst_w, dst_h) ? 2 : 1;
     std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
     if (D.mode == 1) { resize_table(W, dst_w, true, xt); resize_table(H, dst_h, false, yt); }
-    const int tw = cn == 4 ? 32 : 128;
-    for (int y = 0; y < dst_h; y += 8) for (int x = 0; x < dst_w; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
+    const int tw = resize_tile_w(cn), th = resize_tile_h(cn);
+    for (int y = 0; y < dst_h; y += th) for (int x = 0; x < dst_w; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
     DevBuf<uint8_t> d_out; DevBuf<LevelDesc> d_lv; DevBuf<ResizeCoef> d_xt, d_yt; DevBuf<ResizeItem> d_it;
     cudaError_t e = d_out.reserve((size_t)D.pitch * dst_h + 64);
     D.img = d_out.p;

@@ -30,10 +30,13 @@ struct LevelDesc {
     int pad;
 };
 
-// resize coefficient table entry (one per destination column / row of a level):
-// ofs = source index (column or row; rows NOT yet clipped, see resize.cpp:1821-1825),
-// c0/c1 = 11-bit fixed-point weights (resize.cpp:3647-3655)
-struct ResizeCoef { int ofs; short c0, c1; };
+// resize coefficient table entry (one per destination column / row of a level), everything the kernel would
+// otherwise recompute per pixel is folded in on the host:
+//   column entry: s0 = left source column, s1 = min(s0 + 1, W - 1) (its weight is 0 at the right edge),
+//                 c0 = a0 | a1 << 16  (11-bit fixed-point weights, resize.cpp:3647-3655), c1 unused
+//   row entry:    s0 / s1 = the two source rows AFTER the clip of resize.cpp:1821-1825,
+//                 c0 = b0 << 16, c1 = b1 << 16  (so that umulhi(c, t) == (b * t) >> 16)
+struct __align__(16) ResizeCoef { int s0, s1; unsigned c0, c1; };
 
 // work item of the fused gradient+histogram kernel (one warp): a strip of block rows x a tile of block columns
 struct HistItem { short level; short bx0; short by0; short nby; };   // nby = block rows in this strip
@@ -50,6 +53,8 @@ struct BlockWeights { float a0[16]; float a1[16]; };
 struct Candidate { int level; int x; int y; float score; };
 
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------------
+int resize_tile_w(int cn);   // tile geometry the host uses to build ResizeItems
+int resize_tile_h(int cn);
 void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);
