@@ -30,8 +30,12 @@ constexpr int kTileWY = 8;
 constexpr int kRing = kTileWY + 1;           // rows resident: 8 in use + 1 in flight
 constexpr int kMaxWBX = 7;
 constexpr int kRowBlocks = kTileWX + kMaxWBX - 1;          // 38
-constexpr int kRowFloats = kRowBlocks * kHist + 4;         // 1372: /4 = 343, odd -> the 8 window rows of a quarter-warp hit 8 different 16-byte bank groups
+// a ring slot is 11 x 128 B; block row `by_abs` is stored at float offset 4 * (by_abs & 7) inside its slot, so the
+// 8 consecutive block rows that the 8 window rows of a quarter-warp read always sit in 8 different 16-byte bank groups
+constexpr int kRowFloats = 1408;
+static_assert(kRowBlocks * kHist + 28 <= kRowFloats, "ring slot too small");
 constexpr int kMaxCoef = 7 * 15 * kHist;                   // 3780
+constexpr int kRedStride = kTileWX + 1;
 
 struct SvmSmem {
     float ring[kRing][kRowFloats];           // 49,392 B
@@ -43,6 +47,18 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
     unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem));
 }
+// packed FP32 (Blackwell FFMA2): d = a * b + c on both halves
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c)
+{
+    unsigned long long ra, rb, rc, rd;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -53,6 +69,7 @@ __device__ __forceinline__ void load_row(float* dst, const float* __restrict__ p
 {
     const int nvalid = (by_abs < nby) ? max(0, min(kRowBlocks, nbx - bx0)) * (kHist / 4) : 0;   // float4 chunks
     const float4* src = reinterpret_cast<const float4*>(plane + ((long long)by_abs * nbx + bx0) * kHist);
+    dst += 4 * (by_abs & 7);
     for (int i = tid; i < kRowBlocks * (kHist / 4); i += kSvmThreads) {
         if (i < nvalid) cp_async16(dst + 4 * i, src + i);
         else *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -62,7 +79,7 @@ __device__ __forceinline__ void load_row(float* dst, const float* __restrict__ p
 template <int WBX>
 __global__ void __launch_bounds__(kSvmThreads, 3)
 svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
-           const float* __restrict__ hist, const SvmParams P)
+           const float* __restrict__ hist, const __grid_constant__ SvmParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SvmSmem& s = *reinterpret_cast<SvmSmem*>(smem_raw);
@@ -85,9 +102,9 @@ svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ ite
         for (int r = 0; r < kTileWY; r++) load_row(s.ring[r], plane, nbx, nby, wy0 + r, wx0, tid);
         cp_async_commit();
 
-        float acc[kT];
+        float2 acc[kT];         // (even k, odd k) partial sums: two packed FFMA2 per float4 pair
 #pragma unroll
-        for (int j = 0; j < kT; j++) acc[j] = 0.f;
+        for (int j = 0; j < kT; j++) acc[j] = make_float2(0.f, 0.f);
 
         for (int by = 0; by < P.win_by; by++) {
             cp_async_wait_all();
@@ -100,7 +117,7 @@ svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ ite
 #pragma unroll
             for (int bx = 0; bx < WBX; bx++)
                 wv[bx] = *reinterpret_cast<const float4*>(&s.coef[(by * WBX + bx) * kHist + 4 * q]);
-            const float* rowp = &s.ring[(by + ly) % kRing][xg * kT * kHist + 4 * q];
+            const float* rowp = &s.ring[(by + ly) % kRing][4 * ((wy0 + by + ly) & 7) + xg * kT * kHist + 4 * q];
 #pragma unroll
             for (int X = 0; X < kT + WBX - 1; X++) {
                 const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist);
@@ -108,25 +125,23 @@ svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ ite
                 for (int bx = 0; bx < WBX; bx++) {
                     const int j = X - bx;
                     if (j >= 0 && j < kT) {
-                        acc[j] = fmaf(hv.x, wv[bx].x, acc[j]);
-                        acc[j] = fmaf(hv.y, wv[bx].y, acc[j]);
-                        acc[j] = fmaf(hv.z, wv[bx].z, acc[j]);
-                        acc[j] = fmaf(hv.w, wv[bx].w, acc[j]);
+                        acc[j] = fma2(make_float2(hv.x, hv.y), make_float2(wv[bx].x, wv[bx].y), acc[j]);
+                        acc[j] = fma2(make_float2(hv.z, hv.w), make_float2(wv[bx].z, wv[bx].w), acc[j]);
                     }
                 }
             }
         }
         // ---- reduce the 9 k-partials through shared memory (aliases the ring)
         __syncthreads();
-        float* red = &s.ring[0][0];                            // [9][8][32]
+        float* red = &s.ring[0][0];                            // [9][8][33]: odd row stride, the 8 window rows of a store hit 8 banks
 #pragma unroll
-        for (int j = 0; j < kT; j++) red[(q * kTileWY + ly) * kTileWX + xg * kT + j] = acc[j];
+        for (int j = 0; j < kT; j++) red[(q * kTileWY + ly) * kRedStride + xg * kT + j] = acc[j].x + acc[j].y;
         __syncthreads();
         if (tid < kTileWY * kTileWX) {
             const int wy_l = tid >> 5, wx_l = tid & 31;
             float sc = 0.f;
 #pragma unroll
-            for (int k = 0; k < kSvmWarps; k++) sc += red[(k * kTileWY + wy_l) * kTileWX + wx_l];
+            for (int k = 0; k < kSvmWarps; k++) sc += red[(k * kTileWY + wy_l) * kRedStride + wx_l];
             sc += P.bias[d];
             const int vx = wx0 + wx_l, vy = wy0 + wy_l;
             bool valid = vx < vwx && vy < vwy && (vx % P.stride_bx == 0) && (vy % P.stride_by == 0);
