@@ -34,7 +34,7 @@ UNIT = "frames/s"
 CONFIG = {"workload": "cv::cuda::HOG people detector, synthetic 1920x1080 8UC4, nlevels=64, scale 1.05, "
                       "hit_threshold 0, group_threshold 2 (BASELINE configs[1])",
           "frames_per_step_per_gpu": BATCH, "levels": 44, "pyramid_pixels": 21995553, "windows": 261558,
-          "parallelism": "frame-sharded replicas, no collective on the data path",
+          "parallelism": "frame-sharded (frame g -> rank g % N), no collective on the data path, host gather of boxes",
           "l2": "inputs larger than L2 (32 distinct frames = 265 MB per step per GPU)"}
 
 
@@ -163,8 +163,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        host_group = dist.new_group(backend="gloo")        # the host gather of boxes (no collective on the data path)
 
     hog = HOG.create(device=local_rank)
     hog.setSVMDetector(hog.getDefaultPeopleDetector())
@@ -184,7 +186,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(frames, steps):
+    # global frame g of a step lives on rank g % world (opencv_b200/shard.py); this rank holds its BATCH frames
+    my_ids = list(range(rank, BATCH * world, world))
+
+    def timed(frames, steps, gather=False):
         barrier()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         nrects = 0; launches = 0; cands = 0
@@ -194,6 +199,14 @@ def main():
                 out = hog.detectMultiScaleBatch(frames)
                 nrects += sum(len(o) for o in out)
                 t = hog.lastTimings(); launches += t["kernel_launches"]; cands += t["candidates"]
+                if gather and world > 1:                   # boxes of all ranks -> rank 0, frame order, on the host
+                    parts = [None] * world if rank == 0 else None
+                    dist.gather_object(dict(zip(my_ids, out)), parts, dst=0, group=host_group)
+                    if rank == 0:
+                        merged = {}
+                        for q in parts:
+                            merged.update(q)
+                        assert len(merged) == BATCH * world
             e1.record(stream)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
@@ -210,8 +223,8 @@ def main():
     fps = world * BATCH * args.steps / (ms * 1e-3)
 
     # ---- end to end: pinned host frames through the same public call
-    timed(pinned_np, args.warmup)
-    ms_e2e, nrects_e2e, _, cands_e2e = timed(pinned_np, args.steps)
+    timed(pinned_np, args.warmup, gather=True)
+    ms_e2e, nrects_e2e, _, cands_e2e = timed(pinned_np, args.steps, gather=True)
     fps_e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
     h2d = BATCH * W * H * CN
     d2h = int(16 * ((BATCH + 63) // 64) + 16 * max(cands_e2e, 0) / max(args.steps, 1))
@@ -241,9 +254,15 @@ def main():
     except Exception:
         pass
     achieved = alg_bytes / (hist_ms * 1e-3) / 1e9
+    util = {}
+    try:
+        util = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json"))).get("ncu", {})
+    except Exception:
+        pass
     roofline = {"kernel": "hist_kernel<4> (fused gradient + histogram + L2-Hys, all 44 levels in one launch)",
                 "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                "traffic": traffic, "limiter": "instruction issue + shared-memory bandwidth (DESIGN.md 4.1), not HBM",
+                "ncu": util, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": hist_ms,
                 "stage_ms_per_frame": {k: statistics.mean(v) for k, v in ks.items()}}
 
