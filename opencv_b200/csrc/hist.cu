@@ -36,27 +36,33 @@ namespace hogk {
 
 namespace {
 
-constexpr int kWarps = 7;                          // independent workers per CTA (one CTA per SM)
+#ifndef HOGB200_HIST_WARPS
+#define HOGB200_HIST_WARPS 12
+#endif
+#ifndef HOGB200_LUT_COPIES
+#define HOGB200_LUT_COPIES 8
+#endif
+constexpr int kWarps = HOGB200_HIST_WARPS;         // independent workers per CTA (one CTA per SM)
 constexpr int kThreads = kWarps * 32;
 constexpr int kTileCells = 15;                     // 30 voting lanes x 4 columns = 120 columns
 constexpr int kTileBlocks = kTileCells - 1;        // 14 blocks per tile row
 constexpr int kStripBlocks = 8;                    // block rows per work item
-constexpr int kLutCopies = 8;                      // gamma LUT replication (bank spreading)
+constexpr int kLutCopies = HOGB200_LUT_COPIES;     // gamma LUT replication (bank spreading)
 constexpr int kPF = 4;                             // rows of load prefetch
 
-constexpr int kBinBytes = 4 * 32 * 8;              // one accumulator row: [j][idx] float2 = 1024 B
-constexpr int kSlotBytes = kBins * kBinBytes;      // 9216 B
+constexpr int kRows = kBins + 1;                   // accumulator rows per slot: row 9 aliases row 0 (second vote of row 8)
+constexpr int kBinBytes = 4 * 32 * 4;              // one accumulator row: [j][idx] float = 512 B
+constexpr int kSlotBytes = kRows * kBinBytes;      // 5120 B
 constexpr float kMagic = 12582912.f;               // 1.5 * 2^23
 
 struct __align__(16) WarpSmem {
-    float2 acc[3][kBins][4][32];                   // 27,648 B  vertical partial sums, (D,E) pairs
-    float stgD[kTileBlocks * kHist];               //  2,016 B  horizontal results, first-vote plane
-    float stgE[kTileBlocks * kHist];               //  2,016 B  second-vote plane, already shifted to its bin
+    float acc[3][kRows][4][32];                    // 15,360 B  vertical partial sums
+    float stg[kTileBlocks * kHist];                //  2,016 B  horizontal results of one block row
 };
 struct __align__(16) Smem {
     float4 wrow[8];                                //    128 B  vertical weights of row o of a cell row: (R, Q, P/T, -)
     float lut[256 * kLutCopies];                   //  8,192 B  gamma LUT, lut[v*copies + lane%copies]
-    WarpSmem w[kWarps];                            // 7 x 31,680 B
+    WarpSmem w[kWarps];                            // 12 x 17,376 B
 };
 
 // ---- shared-memory access to the accumulators: 32-bit shared addresses, volatile so that the batches below
@@ -70,6 +76,23 @@ __device__ __forceinline__ float2 lds64(unsigned a)
 __device__ __forceinline__ void sts64(unsigned a, float2 v)
 {
     asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a), "f"(v.x), "f"(v.y));
+}
+// one vote = two adjacent accumulator rows (bin0 and bin0 + 1), 512 B apart
+__device__ __forceinline__ float2 lds32x2(unsigned a)
+{
+    float2 v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v.x) : "r"(a));
+    asm volatile("ld.shared.f32 %0, [%1+512];" : "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32x2(unsigned a, float2 v)
+{
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v.x));
+    asm volatile("st.shared.f32 [%0+512], %1;" ::"r"(a), "f"(v.y));
+}
+__device__ __forceinline__ void sts64_zero(unsigned a)
+{
+    asm volatile("st.shared.v2.f32 [%0], {%1,%1};" ::"r"(a), "f"(0.f));
 }
 __device__ __forceinline__ float4 lds128(unsigned a)
 {
@@ -175,19 +198,19 @@ __device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], 
     const unsigned s = (__float_as_uint(dx) ^ __float_as_uint(dy)) & 0x80000000u;
     const float q = __uint_as_float(__float_as_uint(a) ^ s);
     // n = round-to-nearest-even(q) = floor(t) + 1 (a tie only moves a zero vote between two bins);
-    // the mantissa of r holds n, so r << 10 is n * 1024 bytes: the accumulator row of bin floor(t), rows being
+    // the mantissa of r holds n, so r << 9 is n * 512 bytes: the accumulator row of bin floor(t), rows being
     // numbered n + 4 = 0..8 <-> bins 4,5,6,7,8,0,1,2,3 (hog.cpp:531-547 without the wrap)
     const float r = q + kMagic;
     const float nf = r - kMagic;
     const float alpha = (q - nf) + 0.5f;
     Vote v;
-    v.off = __float_as_uint(r) << 10;
+    v.off = __float_as_uint(r) << 9;
     v.g1 = mag * alpha;
     v.g0 = mag - v.g1;
     return v;
 }
 
-// Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row) into the staging planes;
+// Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row) into the staging plane;
 // also zeroes the accumulator for its next use.  lane <-> (accumulator row, cell): 2 rows x 15 cells per pass.
 __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws, int cy, const BlockWeights& W, int lane)
 {
@@ -200,43 +223,41 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
 #pragma unroll
     for (int it = 0; it < 5; it++) {
         const int row = it * 2 + half;
-        const bool act = row < kBins;        // the 10th row slot re-reads row 8 and stores nothing
+        const bool act = row < kBins;        // row 9 only exists as the alias of row 0, folded in below
         // lanes of cell 15 read (and clear) the two halo elements: whatever they hold only reaches sums nobody stores
-        const unsigned base = slot_addr + min(row, kBins - 1) * kBinBytes + cell * 16;
-        float2 v[8];
+        const unsigned base = slot_addr + row * kBinBytes + cell * 8;
+        float v[8];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float4 t = lds128(base + j * 256);              // columns j and 4+j of the cell
-            v[j] = make_float2(t.x, t.y);
-            v[4 + j] = make_float2(t.z, t.w);
+            const float2 t = lds64(base + j * 128);               // columns j and 4+j of the cell
+            v[j] = t.x; v[4 + j] = t.y;
+        }
+        if (it == 0 && half == 0) {          // row 0 += row 9 (second votes of row 8: both are the same bin)
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 t = lds64(base + 9 * kBinBytes + j * 128);
+                v[j] += t.x; v[4 + j] += t.y;
+                sts64_zero(base + 9 * kBinBytes + j * 128);
+            }
         }
         if (act) {
 #pragma unroll
-            for (int j = 0; j < 4; j++) sts128_zero(base + j * 256);
+            for (int j = 0; j < 4; j++) sts64_zero(base + j * 128);
         }
-        float2 s00 = make_float2(0.f, 0.f), s11 = s00, s01 = s00, s10 = s00;
+        float s00 = 0.f, s11 = 0.f, s01 = 0.f, s10 = 0.f;
 #pragma unroll
         for (int p = 0; p < 8; p++) {
-            s00 = fma2(a0[p], v[p], s00);                          // cell k = cx0 of block k
-            s11 = fma2(a18[p], v[p], s11);                         // cell k = cx1 of block k-1
-            if (p < 4) s01 = fma2(a08[p], v[p], s01);              // -> cx0 of block k-1
-            else       s10 = fma2(a1[p - 4], v[p], s10);           // -> cx1 of block k
+            s00 = fmaf(a0[p], v[p], s00);                          // cell k = cx0 of block k
+            s11 = fmaf(a18[p], v[p], s11);                         // cell k = cx1 of block k-1
+            if (p < 4) s01 = fmaf(a08[p], v[p], s01);              // -> cx0 of block k-1
+            else       s10 = fmaf(a1[p - 4], v[p], s10);           // -> cx1 of block k
         }
         // block k, cx=0 = own s00 + s01 of cell k+1 ; block k-1, cx=1 = own s11 + s10 of cell k-1
-        const float ax = s00.x + __shfl_down_sync(0xffffffffu, s01.x, 1);
-        const float ay = s00.y + __shfl_down_sync(0xffffffffu, s01.y, 1);
-        const float bx = s11.x + __shfl_up_sync(0xffffffffu, s10.x, 1);
-        const float by = s11.y + __shfl_up_sync(0xffffffffu, s10.y, 1);
+        const float ax = s00 + __shfl_down_sync(0xffffffffu, s01, 1);
+        const float bx = s11 + __shfl_up_sync(0xffffffffu, s10, 1);
         const int tb = row + 4 >= kBins ? row + 4 - kBins : row + 4;     // bin of this accumulator row
-        const int te = tb + 1 >= kBins ? 0 : tb + 1;                     // the second votes belong to the next bin
-        if (act && cell < kTileBlocks) {
-            ws.stgD[cell * kHist + (0 * 2 + cy) * kBins + tb] = ax;
-            ws.stgE[cell * kHist + (0 * 2 + cy) * kBins + te] = ay;
-        }
-        if (act && cell >= 1 && cell < kTileCells) {
-            ws.stgD[(cell - 1) * kHist + (1 * 2 + cy) * kBins + tb] = bx;
-            ws.stgE[(cell - 1) * kHist + (1 * 2 + cy) * kBins + te] = by;
-        }
+        if (act && cell < kTileBlocks) ws.stg[cell * kHist + (0 * 2 + cy) * kBins + tb] = ax;
+        if (act && cell >= 1 && cell < kTileCells) ws.stg[(cell - 1) * kHist + (1 * 2 + cy) * kBins + tb] = bx;
     }
 }
 
@@ -259,7 +280,7 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         float ss = 0.f;
 #pragma unroll
         for (int b = 0; b < kBins; b++) {
-            v[b] = ws.stgD[idx + b] + ws.stgE[idx + b];
+            v[b] = ws.stg[idx + b];
             ss = fmaf(v[b], v[b], ss);
         }
         ss += __shfl_xor_sync(0xffffffffu, ss, 1);
@@ -277,11 +298,11 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         __syncwarp();       // every lane has read its inputs before any lane overwrites the plane
         if (live) {
 #pragma unroll
-            for (int b = 0; b < kBins; b++) ws.stgD[idx + b] = v[b] * sc2;
+            for (int b = 0; b < kBins; b++) ws.stg[idx + b] = v[b] * sc2;
         }
     }
     __syncwarp();
-    const float4* src = reinterpret_cast<const float4*>(ws.stgD);
+    const float4* src = reinterpret_cast<const float4*>(ws.stg);
     float4* dst = reinterpret_cast<float4*>(out_row);
     for (int i = lane; i < nblk * (kHist / 4); i += 32) dst[i] = src[i];
 }
@@ -311,7 +332,8 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
     // accumulator slots: roles P (block row above, cell row 0), Q (above, cell row 1), R (this, cell row 0);
     // lane l votes into element (l-1)&31 of every [bin][j] row, rows of one slot are 1024 B apart
     const unsigned acc0 = (unsigned)__cvta_generic_to_shared(&ws.acc[0][0][0][0]);
-    const unsigned lane_off = ((lane - 1) & 31) * 8 + 4 * kBinBytes;   // + 4 rows: row index = n + 4
+    // + 4 rows: row index = n + 4; 0x80000000 cancels bit 22 of the magic constant, which `<< 9` leaves in bit 31
+    const unsigned lane_off = ((lane - 1) & 31) * 4 + 4 * kBinBytes + 0x80000000u;
     unsigned sp = acc0, sq = acc0 + kSlotBytes, sr = acc0 + 2 * kSlotBytes;
     zero_slot(sr, lane);                                    // P and Q are cleared during the first cell row
     __syncwarp();
@@ -369,8 +391,8 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
                 unsigned ad[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    ad[j] = v[j].off + lane_off + j * 256;
-                    ar[j] = lds64(ad[j] + sr); aq[j] = lds64(ad[j] + sq); ap[j] = lds64(ad[j] + sp);
+                    ad[j] = v[j].off + lane_off + j * 128;
+                    ar[j] = lds32x2(ad[j] + sr); aq[j] = lds32x2(ad[j] + sq); ap[j] = lds32x2(ad[j] + sp);
                 }
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -378,7 +400,7 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
                     ar[j] = fma2(wr[k], g, ar[j]); aq[j] = fma2(wq[k], g, aq[j]); ap[j] = fma2(wp[k], g, ap[j]);
                 }
 #pragma unroll
-                for (int j = 0; j < 4; j++) { sts64(ad[j] + sr, ar[j]); sts64(ad[j] + sq, aq[j]); sts64(ad[j] + sp, ap[j]); }
+                for (int j = 0; j < 4; j++) { sts32x2(ad[j] + sr, ar[j]); sts32x2(ad[j] + sq, aq[j]); sts32x2(ad[j] + sp, ap[j]); }
 #pragma unroll
                 for (int j = 0; j < 4; j++)
 #pragma unroll

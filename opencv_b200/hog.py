@@ -15,7 +15,8 @@ _LIB = None
 
 
 def lib_path():
-    return os.path.join(_HERE, "libhogb200.so")
+    # HOGB200_LIB: tuning experiments load an alternative build of the same library (tools/build_variant.sh)
+    return os.environ.get("HOGB200_LIB") or os.path.join(_HERE, "libhogb200.so")
 
 
 class HogError(RuntimeError):
