@@ -309,13 +309,17 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
 
 template <int CN>
 __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistItem it, const LevelDesc& L,
-                                             const uint8_t* __restrict__ base, int base_pitch, const BlockWeights& W,
-                                             float l2hys, float* __restrict__ hist, int lane)
+                                             const FrameSet& fs, const BlockWeights& W,
+                                             float l2hys, float* __restrict__ hist_all, int lane)
 {
+    const int frame = it.level >> 8;
+    const uint8_t* __restrict__ base = fs.base[frame];
+    const int base_pitch = fs.pitch[frame];
+    float* __restrict__ hist = hist_all + frame * fs.hist_stride;
     constexpr int NC = CN == 4 ? 3 : 1;
     constexpr int kChunk = 4 * CN;                          // bytes of 4 pixels
     const int w = L.w, h = L.h, pitch = L.img ? L.pitch : base_pitch;
-    const uint8_t* __restrict__ img = L.img ? L.img : base;  // level 0 aliases the frame
+    const uint8_t* __restrict__ img = L.img ? L.img + frame * fs.pyr_stride : base;  // level 0 aliases the frame
     const int xt = it.bx0 * kCell - 4 + 4 * lane;           // first of this lane's 4 columns (lane 0 / 31: halo)
     const int chunk = min(max(xt >> 2, 0), (w - 1) >> 2);   // clamped: out-of-range columns never reach an output
     const uint8_t* __restrict__ colp = img + (size_t)chunk * kChunk;
@@ -424,7 +428,7 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
 
 template <int CN>
 __global__ void __launch_bounds__(kThreads, 1)
-hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* __restrict__ levels,
+hist_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels,
             const HistItem* __restrict__ items, int nitems, unsigned int* __restrict__ queue, int gamma,
             const BlockWeights W, float l2hys, float* __restrict__ hist)
 {
@@ -457,7 +461,8 @@ hist_kernel(const uint8_t* __restrict__ base, int base_pitch, const LevelDesc* _
     while (idx < nitems) {
         const int nidx = fetch();
         const HistItem nit = items[min(nidx, nitems - 1)];
-        process_item<CN>(s, ws, it, levels[it.level], base, base_pitch, W, l2hys, hist, lane);
+        if ((it.level >> 8) < fs.nframes)       // items of absent frames (partial group) are skipped
+            process_item<CN>(s, ws, it, levels[it.level & 255], fs, W, l2hys, hist, lane);
         idx = nidx; it = nit;
     }
     // the last worker to run dry re-arms the queue for the next launch on this stream
@@ -475,12 +480,14 @@ int hist_strip_blocks_y()
     static const int v = [] {
         const char* e = getenv("HOGB200_STRIP");       // tuning knob: block rows per work item
         const int n = e ? atoi(e) : 0;
-        return n > 0 && n <= 512 ? n : kStripBlocks;
+        return n > 0 && n <= 512 ? n : 0;
     }();
     return v;
 }
 
-void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels, const HistItem* d_items,
+int hist_workers_per_sm() { return kWarps; }
+
+void launch_hist(const FrameSet& fs, const LevelDesc* d_levels, const HistItem* d_items,
                  int nitems, unsigned int* d_queue, int num_sms, int cn, int gamma, const BlockWeights& bw, float l2hys,
                  float* d_hist, cudaStream_t st)
 {
@@ -489,10 +496,10 @@ void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels,
     // per-device attribute (cheap host call); the handle may live on any device
     if (cn == 4) {
         cudaFuncSetAttribute(hist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-        hist_kernel<4><<<grid, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
+        hist_kernel<4><<<grid, kThreads, sizeof(Smem), st>>>(fs, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
     } else {
         cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
-        hist_kernel<1><<<grid, kThreads, sizeof(Smem), st>>>(base, base_pitch, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
+        hist_kernel<1><<<grid, kThreads, sizeof(Smem), st>>>(fs, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
     }
 }
 

@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -80,6 +81,9 @@ struct Plan {
     int W = 0, H = 0, cn = 0;
     int nlevels_param = 0; double scale0 = 0; int win_w = 0, win_h = 0, sx = 0, sy = 0;
     bool single_level = false;
+    int group = 1;                       // frames per launch the work lists were built for
+    long long pyr_stride = 0, hist_stride = 0;   // per-frame strides inside d_pyr (bytes) / d_hist (floats)
+    int strip = 0;                       // block rows per histogram work item (chosen by balance_strip)
     std::vector<LevelHost> lv;
     long long hist_floats = 0, score_floats = 0, pyr_pixels = 0, nblocks = 0, nwindows = 0;
     size_t pyr_bytes = 0;
@@ -105,14 +109,14 @@ struct hogb200 {
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
     cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
     // workspace
-    DevBuf<uint8_t> d_frame[2]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
+    DevBuf<uint8_t> d_frame[2 * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
     DevBuf<unsigned int> d_queue;   // work-queue counters of the fused histogram kernel (self re-arming)
     int num_sms = 148;
     DevBuf<unsigned char> d_cand;   // [16-byte header: counter][Candidate * cap]
     size_t cand_cap = 0;
     PinBuf<unsigned char> h_cand;
     DevBuf<float> d_desc;
-    Plan plan, plan1;               // multi-scale plan and single-scale plan
+    Plan plan, plan1, plan_grp;     // multi-scale plan, single-scale plan, multi-scale plan of the batch path (frame groups)
     // timing
     int timing = 0; cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     hogb200_timings last = {};
@@ -202,14 +206,45 @@ bool is_exact_half(int src_w, int src_h, int dst_w, int dst_h)
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
+// Block rows per histogram work item.  The kernel's workers (warps) pull items longest-first from a queue, so the
+// finishing time is that of greedy list scheduling: simulate it for every candidate height and keep the best
+// (a taller strip recomputes less -- one cell row per strip is shared with the strip above -- but balances worse).
+int balance_strip(const std::vector<LevelHost>& lv, int group, int workers)
 {
-    if (P.valid && P.W == W && P.H == H && P.cn == cn && P.single_level == single &&
+    if (hist_strip_blocks_y() > 0) return hist_strip_blocks_y();
+    const int tbx = hist_tile_blocks_x();
+    int best = 8; double best_t = 1e300;
+    for (int S = 4; S <= 16; S++) {
+        std::vector<int> cost;
+        for (const LevelHost& L : lv)
+            for (int by = 0; by < L.nby; by += S)
+                for (int bx = 0; bx < L.nbx; bx += tbx) cost.push_back(std::min(S, L.nby - by) + 2);   // + shared cell row + set-up
+        std::sort(cost.begin(), cost.end(), std::greater<int>());
+        std::vector<long long> heap(workers, 0);          // min-heap of worker finishing times
+        auto cmp = std::greater<long long>();
+        for (int g = 0; g < group; g++)
+            for (int c : cost) {
+                std::pop_heap(heap.begin(), heap.end(), cmp);
+                heap.back() += c;
+                std::push_heap(heap.begin(), heap.end(), cmp);
+            }
+        // the model assumes a worker's speed does not depend on how many others are running; that only holds with a
+        // few items per worker, so strips that leave fewer than ~2 items per worker are not considered
+        if ((long long)cost.size() * group < (long long)workers * 9 / 5 && S > 4) continue;
+        const double t = (double)*std::max_element(heap.begin(), heap.end());
+        if (t <= best_t) { best_t = t; best = S; }
+    }
+    return best;
+}
+
+int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group = 1)
+{
+    if (P.valid && P.W == W && P.H == H && P.cn == cn && P.single_level == single && P.group == group &&
         P.nlevels_param == h->nlevels && P.scale0 == h->scale0 && P.win_w == h->g.win_w && P.win_h == h->g.win_h &&
         P.sx == h->win_stride_x && P.sy == h->win_stride_y && P.pyr_base == h->d_pyr.p)
         return HOGB200_OK;
     P.valid = false;
-    P.W = W; P.H = H; P.cn = cn; P.single_level = single;
+    P.W = W; P.H = H; P.cn = cn; P.single_level = single; P.group = group;
     P.nlevels_param = h->nlevels; P.scale0 = h->scale0; P.win_w = h->g.win_w; P.win_h = h->g.win_h;
     P.sx = h->win_stride_x; P.sy = h->win_stride_y;
 
@@ -256,10 +291,6 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
         }
         D.w = L.w; D.h = L.h; D.nbx = L.nbx; D.nby = L.nby; D.nwx = L.nwx; D.nwy = L.nwy;
         D.hist_off = L.hist_off; D.score_off = L.score_off; D.mode = L.mode; D.pitch = L.pitch;
-        const int tbx = hist_tile_blocks_x(), sby_ = hist_strip_blocks_y();
-        for (int by = 0; by < L.nby; by += sby_)
-            for (int bx = 0; bx < L.nbx; bx += tbx)
-                hitems.push_back(HistItem{(short)i, (short)bx, (short)by, (short)std::min(sby_, L.nby - by)});
         const int vwx = L.nbx - wbx + 1, vwy = L.nby - wby + 1;
         if (L.nwx > 0 && vwx > 0 && vwy > 0)
             for (int wy = 0; wy < vwy; wy += svm_tile_wy())
@@ -267,16 +298,35 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single)
         P.lv.push_back(L); descs.push_back(D);
     }
     (void)sbx; (void)sby;
-    // the histogram kernel's workers pull items from a queue: longest first, so that the tail is made of short ones
+    // histogram work items: strips of P.strip block rows x tiles of 14 blocks, for every frame of the group;
+    // the kernel's workers pull them from a queue, longest first, so that the tail is made of short ones
+    P.strip = balance_strip(P.lv, group, h->num_sms * hist_workers_per_sm());
+    for (size_t i = 0; i < P.lv.size(); i++) {
+        const LevelHost& L = P.lv[i];
+        const int tbx = hist_tile_blocks_x();
+        for (int by = 0; by < L.nby; by += P.strip)
+            for (int bx = 0; bx < L.nbx; bx += tbx)
+                hitems.push_back(HistItem{(short)i, (short)bx, (short)by, (short)std::min(P.strip, L.nby - by)});
+    }
     std::stable_sort(hitems.begin(), hitems.end(), [](const HistItem& a, const HistItem& b) {
         return a.nby > b.nby;       // a partial tile costs a warp as much as a full one
     });
+    // replicate the lists for frames 1 .. group-1 (frame-minor, so that equal-sized items of all frames are adjacent)
+    if (group > 1) {
+        std::vector<ResizeItem> r2; std::vector<HistItem> h2; std::vector<SvmItem> s2;
+        for (const ResizeItem& it : ritems) for (int f = 0; f < group; f++) { ResizeItem t = it; t.frame = (short)f; r2.push_back(t); }
+        for (const HistItem& it : hitems) for (int f = 0; f < group; f++) { HistItem t = it; t.level = (short)(it.level | (f << 8)); h2.push_back(t); }
+        for (const SvmItem& it : sitems) for (int f = 0; f < group; f++) { SvmItem t = it; t.frame = (short)f; s2.push_back(t); }
+        ritems.swap(r2); hitems.swap(h2); sitems.swap(s2);
+    }
+    P.pyr_stride = (long long)align_up(pyr, 256);
+    P.hist_stride = P.hist_floats;
     P.pyr_bytes = pyr;
-    CK(h->d_pyr.reserve(pyr + 256));
+    CK(h->d_pyr.reserve((size_t)P.pyr_stride * group + 256));
     for (size_t i = 0; i < descs.size(); i++)
         if (P.lv[i].mode != 0) descs[i].img = h->d_pyr.p + P.lv[i].img_off;
     P.pyr_base = h->d_pyr.p;
-    CK(h->d_hist.reserve((size_t)P.hist_floats + 64));
+    CK(h->d_hist.reserve((size_t)P.hist_stride * group + 64));
     P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size();
     cudaStream_t st = h->stream;
     CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use
@@ -342,19 +392,22 @@ int ensure_cand(hogb200* h, size_t cap)
     return HOGB200_OK;
 }
 
-// Queue the three kernels of one frame on the handle's stream.
-int queue_frame(hogb200* h, Plan& P, FrameRef f, int ndet, const int* slots, float thresh, float* d_scores,
-                int tag, int* launches)
+// Queue the three kernels for a group of frames (1 .. P.group) on the handle's stream.
+int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, const int* slots, float thresh,
+                float* d_scores, int tag, int* launches)
 {
     cudaStream_t st = h->stream;
+    FrameSet fs; memset(&fs, 0, sizeof fs);
+    for (int i = 0; i < nframes; i++) { fs.base[i] = f[i].dev; fs.pitch[i] = f[i].pitch; }
+    fs.nframes = nframes; fs.pyr_stride = P.pyr_stride; fs.hist_stride = P.hist_stride;
     if (h->timing) cudaEventRecord(h->ev[1], st);
     if (P.n_resize) {
-        launch_resize(f.dev, f.pitch, P.W, P.H, P.cn, P.d_levels.p, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
+        launch_resize(fs, P.W, P.H, P.cn, P.d_levels.p, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
         (*launches)++;
     }
     if (h->timing) cudaEventRecord(h->ev[2], st);
     if (P.n_hist) {
-        launch_hist(f.dev, f.pitch, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
+        launch_hist(fs, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
                     make_weights(h->win_sigma), (float)h->l2hys, h->d_hist.p, st);
         (*launches)++;
     }
@@ -369,7 +422,7 @@ int queue_frame(hogb200* h, Plan& P, FrameRef f, int ndet, const int* slots, flo
         sp.cand = reinterpret_cast<Candidate*>(h->d_cand.p + 16);
         sp.cand_count = reinterpret_cast<unsigned int*>(h->d_cand.p);
         sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
-        launch_svm(P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, st);
+        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, st);
         (*launches)++;
     }
     if (h->timing) cudaEventRecord(h->ev[4], st);
@@ -581,9 +634,10 @@ void hogb200_destroy(hogb200_t* h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (int i = 0; i < kMaxDet; i++) h->d_det[i].release();
-    h->d_frame[0].release(); h->d_frame[1].release(); h->d_pyr.release(); h->d_hist.release();
+    for (auto& b : h->d_frame) b.release();
+    h->d_pyr.release(); h->d_hist.release();
     h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
-    for (Plan* P : {&h->plan, &h->plan1}) {
+    for (Plan* P : {&h->plan, &h->plan1, &h->plan_grp}) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();
     }
@@ -673,6 +727,17 @@ int check_work_params(const hogb200* h)
     return HOGB200_OK;
 }
 
+// frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup)
+int batch_group()
+{
+    static const int v = [] {
+        const char* e = getenv("HOGB200_GROUP");
+        const int n = e ? atoi(e) : 0;
+        return n >= 1 && n <= kMaxGroup ? n : 4;
+    }();
+    return v;
+}
+
 // One frame through the pipeline; candidates come back sorted by (detector, level, y, x).
 int run_single(hogb200* h, Plan& P, const hogb200_image* img, bool single, int ndet, const int* slots,
                float thresh, float* d_scores, std::vector<Candidate>& cands)
@@ -694,7 +759,7 @@ int run_single(hogb200* h, Plan& P, const hogb200_image* img, bool single, int n
         CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
         FrameRef f;
         if ((rc = stage_frame(h, img, 0, st, f))) return rc;
-        if ((rc = queue_frame(h, P, f, ndet, slots, thresh, d_scores, 0, &launches))) return rc;
+        if ((rc = queue_group(h, P, &f, 1, ndet, slots, thresh, d_scores, 0, &launches))) return rc;
         size_t n = 0;
         rc = fetch_candidates(h, cands, &n);
         if (h->timing) cudaEventRecord(h->ev[5], st);
@@ -795,26 +860,33 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         while (f0 + nf < nframes && nf < kChunk && frames[f0 + nf].width == frames[f0].width &&
                frames[f0 + nf].height == frames[f0].height && frames[f0 + nf].channels == frames[f0].channels) nf++;
         const hogb200_image* fr = &frames[f0];
-        if ((rc = build_plan(h, h->plan, fr->width, fr->height, fr->channels, false))) return rc;
-        Plan& P = h->plan;
+        // frames go through the kernels in groups: one launch of each kernel covers `grp` frames, which evens out the
+        // tail of the persistent histogram kernel and the last wave of the other two
+        const int grp = std::min(batch_group(), nf);
+        if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels, false, grp))) return rc;
+        Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
         for (int attempt = 0; attempt < 2; attempt++) {
             if ((rc = ensure_cand(h, cap))) return rc;
             CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
-            for (int i = 0; i < nf; i++) {
-                const hogb200_image* im = fr + i;
-                const int b = i & 1;
-                FrameRef f;
-                if (!im->on_device) {
-                    // double-buffered upload on the copy stream, overlapping the previous frame's kernels
-                    CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
-                    if ((rc = stage_frame(h, im, b, cs, f))) return rc;
+            for (int g0 = 0, gi = 0; g0 < nf; g0 += grp, gi++) {
+                const int ng = std::min(grp, nf - g0);
+                const int b = gi & 1;                     // double-buffered staging, per group
+                FrameRef f[kMaxGroup];
+                bool any_host = false;
+                for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
+                if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
+                else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
+                for (int j = 0; j < ng; j++) {
+                    const hogb200_image* im = fr + g0 + j;
+                    // host frames: upload on the copy stream, overlapping the previous group's kernels
+                    if ((rc = stage_frame(h, im, b * kMaxGroup + j, im->on_device ? st : cs, f[j]))) return rc;
+                }
+                if (any_host) {
                     CK(cudaEventRecord(h->up_done[b], cs));
                     CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
-                } else {
-                    if ((rc = stage_frame(h, im, b, st, f))) return rc;
                 }
-                if ((rc = queue_frame(h, P, f, nslots, slots, (float)h->hit_threshold, nullptr, i << 20, &total_launches))) return rc;
+                if ((rc = queue_group(h, P, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches))) return rc;
                 CK(cudaEventRecord(h->fr_done[b], st));
             }
             size_t n = 0;
@@ -838,7 +910,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         f0 += nf;
     }
     if (h->timing) cudaEventRecord(h->ev[5], st);
-    finish_timing(h, h->plan, total_launches, all.size());
+    finish_timing(h, h->plan_grp, total_launches, all.size());
     size_t cnt = 0;
     return emit(all, found, capacity, &cnt);
 }
@@ -934,7 +1006,9 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
     if (e == cudaSuccess && !yt.empty()) e = cudaMemcpyAsync(d_yt.p, yt.data(), yt.size() * sizeof(ResizeCoef), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_it.p, items.data(), items.size() * sizeof(ResizeItem), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) {
-        launch_resize(f.dev, f.pitch, W, H, cn, d_lv.p, d_xt.p, d_yt.p, d_it.p, (int)items.size(), st);
+        FrameSet fs; memset(&fs, 0, sizeof fs);
+        fs.base[0] = f.dev; fs.pitch[0] = f.pitch; fs.nframes = 1;
+        launch_resize(fs, W, H, cn, d_lv.p, d_xt.p, d_yt.p, d_it.p, (int)items.size(), st);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaMemcpy2DAsync(out, row, d_out.p, D.pitch, row, dst_h, cudaMemcpyDeviceToHost, st);

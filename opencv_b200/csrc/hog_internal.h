@@ -15,6 +15,18 @@ constexpr int kBins = 9;
 constexpr int kHist = 36;            // floats per block histogram
 constexpr int kMaxLevels = 256;
 constexpr int kMaxDet = 4;
+constexpr int kMaxGroup = 8;         // frames one launch of each kernel can process (frame groups of the batch path)
+
+// The frames of one group.  Frame f keeps its pyramid levels at LevelDesc::img + f * pyr_stride and its block
+// histograms at hist + f * hist_stride; level 0 aliases base[f].  Work items carry the frame index.
+struct FrameSet {
+    const uint8_t* base[kMaxGroup];
+    int pitch[kMaxGroup];
+    int nframes;                     // items of frames >= nframes are skipped (partial group)
+    int pad;
+    long long pyr_stride;            // bytes
+    long long hist_stride;           // floats
+};
 
 // One pyramid level of one frame.  Lives in device memory (array indexed by level).
 struct LevelDesc {
@@ -38,12 +50,13 @@ struct LevelDesc {
 //                 c0 = b0 << 16, c1 = b1 << 16  (so that umulhi(c, t) == (b * t) >> 16)
 struct __align__(16) ResizeCoef { int s0, s1; unsigned c0, c1; };
 
-// work item of the fused gradient+histogram kernel (one warp): a strip of block rows x a tile of block columns
+// work item of the fused gradient+histogram kernel (one warp): a strip of block rows x a tile of block columns;
+// level = pyramid level | frame-in-group << 8
 struct HistItem { short level; short bx0; short by0; short nby; };   // nby = block rows in this strip
-// work item of the SVM kernel: a tile of windows of one level
-struct SvmItem { short level; short wx0; short wy0; short pad; };
-// work item of the resize kernel: 8 destination rows x a span of columns
-struct ResizeItem { short level; short x0; short y0; short pad; };
+// work item of the SVM kernel: a tile of windows of one level of one frame
+struct SvmItem { short level; short wx0; short wy0; short frame; };
+// work item of the resize kernel: a tile of destination pixels of one level of one frame
+struct ResizeItem { short level; short x0; short y0; short frame; };
 
 // separable block window: vertical (or horizontal) weight of pixel offset i in [0,16) for cell 0 / cell 1 of
 // the block: gauss(i) * bilinear cell weight (HOGCache::init, objdetect/src/hog.cpp:653-839)
@@ -55,7 +68,7 @@ struct Candidate { int level; int x; int y; float score; };
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------------
 int resize_tile_w(int cn);   // tile geometry the host uses to build ResizeItems
 int resize_tile_h(int cn);
-void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
+void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);
 
@@ -63,9 +76,10 @@ void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
 // d_queue: two zero-initialised counters in device memory (work queue head, finished workers); the kernel
 // re-arms them itself, so consecutive launches on one stream need no host reset.  Rows of the level images
 // must be 16-byte aligned for cn == 4 (4-byte for cn == 1).
-void launch_hist(const uint8_t* base, int base_pitch, const LevelDesc* d_levels, const HistItem* d_items,
+void launch_hist(const FrameSet& fs, const LevelDesc* d_levels, const HistItem* d_items,
                  int nitems, unsigned int* d_queue, int num_sms, int cn, int gamma, const BlockWeights& bw,
                  float l2hys, float* d_hist, cudaStream_t st);
+int hist_workers_per_sm();  // warps pulling items from the queue, per SM (the host balances the item list for them)
 
 struct SvmParams {
     int win_bx, win_by;        // window size in blocks (7 x 15)
@@ -81,7 +95,7 @@ struct SvmParams {
     unsigned int cand_cap;
     int tag;                   // OR-ed into Candidate::level: frame-in-chunk << 20 (detector goes to bits 16..19)
 };
-void launch_svm(const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
+void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
                 const SvmParams& p, cudaStream_t st);
 int svm_tile_wx();   // tile geometry the host uses to build SvmItems
 int svm_tile_wy();
@@ -90,6 +104,6 @@ void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_
                     int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);
 
 int hist_tile_blocks_x();   // blocks per tile in x (14)
-int hist_strip_blocks_y();  // block rows per strip
+int hist_strip_blocks_y();  // block rows per strip: 0 = let the host choose, else the HOGB200_STRIP override
 
 }  // namespace hogk

@@ -45,18 +45,21 @@ __device__ __forceinline__ HRow hrow_c4(const uint8_t* __restrict__ row, int sx0
 }
 
 __global__ void __launch_bounds__(256)
-resize_c4_kernel(const uint8_t* __restrict__ base, int bpitch, int bw, int bh,
+resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
                  const LevelDesc* __restrict__ levels, const ResizeCoef* __restrict__ xtab,
                  const ResizeCoef* __restrict__ ytab, const ResizeItem* __restrict__ items)
 {
     const ResizeItem it = items[blockIdx.x];
+    if (it.frame >= fs.nframes) return;
+    const uint8_t* __restrict__ base = fs.base[it.frame];
+    const int bpitch = fs.pitch[it.frame];
     const LevelDesc& L = levels[it.level];
     const int x = it.x0 + (threadIdx.x & 31);
     const int y0 = it.y0 + (threadIdx.x >> 5) * kC4RowsPerWarp;
     const int w = L.w, h = L.h;
     if (x >= w || y0 >= h) return;
     const int y1 = min(y0 + kC4RowsPerWarp, h);
-    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + (size_t)y0 * L.pitch + 4 * x;
+    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y0 * L.pitch + 4 * x;
     const int dpitch = L.pitch;
     if (L.mode == 2) {          // exact half: 2x2 box average (resize.cpp:2542-2578)
         for (int y = y0; y < y1; y++, dst += dpitch) {
@@ -116,11 +119,14 @@ resize_c4_kernel(const uint8_t* __restrict__ base, int bpitch, int bw, int bh,
 
 // 8UC1: one thread = four consecutive destination pixels (one 4-byte store); tile 128 x 8.
 __global__ void __launch_bounds__(256)
-resize_c1_kernel(const uint8_t* __restrict__ base, int bpitch, int bw, int bh,
+resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
                  const LevelDesc* __restrict__ levels, const ResizeCoef* __restrict__ xtab,
                  const ResizeCoef* __restrict__ ytab, const ResizeItem* __restrict__ items)
 {
     const ResizeItem it = items[blockIdx.x];
+    if (it.frame >= fs.nframes) return;
+    const uint8_t* __restrict__ base = fs.base[it.frame];
+    const int bpitch = fs.pitch[it.frame];
     const LevelDesc& L = levels[it.level];
     const int x4 = it.x0 + 4 * (threadIdx.x & 31), y = it.y0 + (threadIdx.x >> 5);
     if (x4 >= L.w || y >= L.h) return;
@@ -151,7 +157,7 @@ resize_c1_kernel(const uint8_t* __restrict__ base, int bpitch, int bw, int bh,
             }
         }
     }
-    uint8_t* dst = const_cast<uint8_t*>(L.img) + (size_t)y * L.pitch + x4;
+    uint8_t* dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y * L.pitch + x4;
     if (x4 + 3 < L.w) {
         *reinterpret_cast<uchar4*>(dst) = make_uchar4(o[0], o[1], o[2], o[3]);   // level pitch is a multiple of 16
     } else {
@@ -164,15 +170,15 @@ resize_c1_kernel(const uint8_t* __restrict__ base, int bpitch, int bw, int bh,
 int resize_tile_w(int cn) { return cn == 4 ? kC4TileW : 128; }
 int resize_tile_h(int cn) { return cn == 4 ? kC4TileH : 8; }
 
-void launch_resize(const uint8_t* base, int base_pitch, int bw, int bh, int cn,
+void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st)
 {
     if (nitems <= 0) return;
     if (cn == 4)
-        resize_c4_kernel<<<nitems, 256, 0, st>>>(base, base_pitch, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+        resize_c4_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
     else
-        resize_c1_kernel<<<nitems, 256, 0, st>>>(base, base_pitch, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+        resize_c1_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
 }
 
 }  // namespace hogk

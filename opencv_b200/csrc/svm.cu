@@ -78,7 +78,7 @@ __device__ __forceinline__ void load_row(float* dst, const float* __restrict__ p
 
 template <int WBX>
 __global__ void __launch_bounds__(kSvmThreads, 3)
-svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
+svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
            const float* __restrict__ hist, const __grid_constant__ SvmParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -87,8 +87,9 @@ svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ ite
     const int ly = lane & 7, xg = lane >> 3;
 
     const SvmItem it = items[blockIdx.x];
+    if (it.frame >= fs.nframes) return;
     const LevelDesc& L = levels[it.level];
-    const float* plane = hist + L.hist_off;
+    const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
     const int nbx = L.nbx, nby = L.nby;
     // dense (stride-1) window grid of the level; the requested stride subsamples it at output time
     const int vwx = nbx - WBX + 1, vwy = nby - P.win_by + 1;
@@ -156,7 +157,7 @@ svm_kernel(const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ ite
                 if (hit) {
                     const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
                     if (pos < P.cand_cap) {
-                        Candidate c; c.level = it.level | (d << 16) | P.tag; c.x = ox; c.y = oy; c.score = sc;
+                        Candidate c; c.level = it.level | (d << 16) | (P.tag + (it.frame << 20)); c.x = ox; c.y = oy; c.score = sc;
                         P.cand[pos] = c;
                     }
                 }
@@ -190,16 +191,16 @@ __global__ void extract_kernel(const LevelDesc* __restrict__ level, const float*
 int svm_tile_wx() { return kTileWX; }
 int svm_tile_wy() { return kTileWY; }
 
-void launch_svm(const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
+void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
                 const SvmParams& p, cudaStream_t st)
 {
     if (nitems <= 0 || p.ndet <= 0) return;
     if (p.win_bx == 7) {
         cudaFuncSetAttribute(svm_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<7><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(d_levels, d_items, d_hist, p);
+        svm_kernel<7><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, d_hist, p);
     } else if (p.win_bx == 5) {
         cudaFuncSetAttribute(svm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<5><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(d_levels, d_items, d_hist, p);
+        svm_kernel<5><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, d_hist, p);
     }
 }
 
