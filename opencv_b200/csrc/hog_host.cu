@@ -285,7 +285,8 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
             L.img_off = pyr; pyr += align_up((size_t)L.pitch * L.h, 256);
             D.xtab_off = (int)xtab.size(); D.ytab_off = (int)ytab.size();
             if (L.mode == 1) { resize_table(W, L.w, true, xtab); resize_table(H, L.h, false, ytab); }
-            const int tw = resize_tile_w(cn), th = resize_tile_h(cn);
+            if (L.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(&xtab[D.xtab_off], L.w, &ytab[D.ytab_off], L.h, W);
+            const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
             for (int y = 0; y < L.h; y += th)
                 for (int x = 0; x < L.w; x += tw) ritems.push_back(ResizeItem{(short)i, (short)x, (short)y, 0});
         }
@@ -992,7 +993,8 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
     D.mode = is_exact_half(W, H, dst_w, dst_h) ? 2 : 1;
     std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
     if (D.mode == 1) { resize_table(W, dst_w, true, xt); resize_table(H, dst_h, false, yt); }
-    const int tw = resize_tile_w(cn), th = resize_tile_h(cn);
+    if (D.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(xt.data(), dst_w, yt.data(), dst_h, W);
+    const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
     for (int y = 0; y < dst_h; y += th) for (int x = 0; x < dst_w; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
     DevBuf<uint8_t> d_out; DevBuf<LevelDesc> d_lv; DevBuf<ResizeCoef> d_xt, d_yt; DevBuf<ResizeItem> d_it;
     cudaError_t e = d_out.reserve((size_t)D.pitch * dst_h + 64);

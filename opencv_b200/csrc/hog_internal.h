@@ -39,7 +39,7 @@ struct LevelDesc {
     long long score_off;  // float offset of this level's [nwy][nwx] plane in the score buffer
     int xtab_off, ytab_off;  // offsets into the resize coefficient tables (entries)
     int mode;             // 0 = alias/copy of base, 1 = bilinear, 2 = exact-2x area
-    int pad;
+    int rs_rows;          // 8UC4 resize: destination rows per warp and staging scheme (resize_plan_rows)
 };
 
 // resize coefficient table entry (one per destination column / row of a level), everything the kernel would
@@ -67,7 +67,8 @@ struct Candidate { int level; int x; int y; float score; };
 
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------------
 int resize_tile_w(int cn);   // tile geometry the host uses to build ResizeItems
-int resize_tile_h(int cn);
+int resize_tile_h(int cn, int rs_rows);
+int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w);
 void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);

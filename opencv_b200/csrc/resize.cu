@@ -9,12 +9,12 @@
 // Coefficients come from small per-level tables built on the host in double precision exactly as the reference
 // builds them, so the kernel is integer-only.
 #include "hog_internal.h"
+#include <algorithm>
 
 namespace hogk {
 
 namespace {
 
-__device__ __forceinline__ int clipi(int x, int a, int b) { return x >= a ? (x < b ? x : b - 1) : a; }
 
 __device__ __forceinline__ int vlin(int h0, int h1, int b0, int b1)
 {
@@ -22,18 +22,30 @@ __device__ __forceinline__ int vlin(int h0, int h1, int b0, int b1)
     return (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
 }
 
-// 8UC4: a CTA owns a tile of 32 columns x 64 rows; thread <-> column, each warp walks DOWN 8 rows.
-// The horizontal pass of a source row (resize.cpp:1491-1542) is kept in registers and reused by the next
-// destination row when it needs the same source row (always the case for scales below ~1.5, i.e. for most of the
-// pyramid's pixels); both taps of a channel are one IDP.2A (16-bit weights x 8-bit samples).
-constexpr int kC4TileW = 32, kC4RowsPerWarp = 8, kC4TileH = 8 * kC4RowsPerWarp;
+// 8UC4.  A warp owns 64 columns x R rows of a level (lane <-> columns x and x + 32) and walks DOWN the rows.
+//   * Staging: the source rows the warp needs (columns [c_lo, c_lo + span)) are brought into its private slice of
+//     shared memory by bulk async copies (cp.async.bulk, one per source row, completion on the warp's own
+//     mbarrier), so the inner loop addresses pixels with 32-bit shared offsets and never waits on L2.  For
+//     scales < 2 the rows are one contiguous range; for scales >= 2 (no source row is shared by two destination
+//     rows) only the two rows of every destination row are staged.  R is chosen per level on the host so that the
+//     slice fits (resize_plan_rows); levels too coarse even for R = 1 read global memory directly.
+//   * The horizontal pass of a source row (resize.cpp:1491-1542) stays in registers and is reused by the next
+//     destination row when it needs the same source row (always the case below scale ~1.5, i.e. for most of the
+//     pyramid's pixels); both taps of a channel are one IDP.2A (16-bit weights x 8-bit samples).
+//   * Vertical pass + pack: the two truncated products of channels c and c+2 are packed by IMADs into 16-bit
+//     fields, rounded and shifted together, and one PRMT assembles the four bytes.
+constexpr int kRsWarps = 4;
+constexpr int kRsTileW = 64;
+constexpr int kRsMaxRows = 16;                              // destination rows per warp, at most
+constexpr int kRsHeader = 16 + 16 * kRsMaxRows;             // mbarrier + per-row coefficients
+constexpr int kRsWarpBytes = 6144;                          // staged source pixels per warp
+constexpr int kRsWarpStride = kRsHeader + kRsWarpBytes;
+constexpr int kRsDirectRows = 8;                            // rows per warp of the unstaged paths
 
 struct HRow { int t[4]; };        // horizontal result >> 4 of the four channels (resize.cpp:1596: S0[x] >> 4)
 
-__device__ __forceinline__ HRow hrow_c4(const uint8_t* __restrict__ row, int sx0, int sx1, unsigned a01)
+__device__ __forceinline__ HRow hrow_px(unsigned p0, unsigned p1, unsigned a01)
 {
-    const unsigned p0 = __ldg(reinterpret_cast<const unsigned*>(row) + sx0);
-    const unsigned p1 = __ldg(reinterpret_cast<const unsigned*>(row) + sx1);
     const unsigned lo = __byte_perm(p0, p1, 0x5140);     // (p0.b0, p1.b0, p0.b1, p1.b1)
     const unsigned hi = __byte_perm(p0, p1, 0x7362);     // (p0.b2, p1.b2, p0.b3, p1.b3)
     HRow h;
@@ -43,77 +55,179 @@ __device__ __forceinline__ HRow hrow_c4(const uint8_t* __restrict__ row, int sx0
     h.t[3] = (int)(__dp2a_hi(a01, hi, 0u) >> 4);
     return h;
 }
+__device__ __forceinline__ HRow hrow_gmem(const uint8_t* __restrict__ row, int sx0, int sx1, unsigned a01)
+{
+    return hrow_px(__ldg(reinterpret_cast<const unsigned*>(row) + sx0), __ldg(reinterpret_cast<const unsigned*>(row) + sx1), a01);
+}
+__device__ __forceinline__ HRow hrow_smem(unsigned addr, unsigned a01)
+{
+    unsigned p0, p1;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(p0) : "r"(addr));
+    asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(p1) : "r"(addr));       // weight 0 where sx + 1 is outside the row
+    return hrow_px(p0, p1, a01);
+}
+// resize.cpp:1594-1601: uchar(( ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2) for four channels; b0/b1 come
+// pre-shifted by 16 so that umulhi is the truncating product.  All fields stay below 2^11, so channels c and c+2
+// share a register from the first addition on.
+__device__ __forceinline__ unsigned vertical_pack(const HRow& h0, const HRow& h1, unsigned b0, unsigned b1)
+{
+    const unsigned p02 = (__umulhi(b0, (unsigned)h0.t[2]) * 65536u + __umulhi(b0, (unsigned)h0.t[0])) +
+                         (__umulhi(b1, (unsigned)h1.t[2]) * 65536u + __umulhi(b1, (unsigned)h1.t[0])) + 0x00020002u;
+    const unsigned p13 = (__umulhi(b0, (unsigned)h0.t[3]) * 65536u + __umulhi(b0, (unsigned)h0.t[1])) +
+                         (__umulhi(b1, (unsigned)h1.t[3]) * 65536u + __umulhi(b1, (unsigned)h1.t[1])) + 0x00020002u;
+    return __byte_perm(p02 >> 2, p13 >> 2, 0x6240);
+}
 
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned mbar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(mbar), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (16-byte aligned on both sides, size a multiple of 16), completion counted in bytes on mbar
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+
+// One destination row of the unstaged bilinear path (levels too coarse to stage): both taps from global memory.
+__device__ __forceinline__ unsigned direct_px(const uint8_t* __restrict__ base, int bpitch, const ResizeCoef& cx,
+                                              const ResizeCoef& cy)
+{
+    const HRow h0 = hrow_gmem(base + (size_t)cy.s0 * bpitch, cx.s0, cx.s1, cx.c0);
+    const HRow h1 = hrow_gmem(base + (size_t)cy.s1 * bpitch, cx.s0, cx.s1, cx.c0);
+    return vertical_pack(h0, h1, cy.c0, cy.c1);
+}
+
+__global__ void __launch_bounds__(kRsWarps * 32)
 resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
                  const LevelDesc* __restrict__ levels, const ResizeCoef* __restrict__ xtab,
                  const ResizeCoef* __restrict__ ytab, const ResizeItem* __restrict__ items)
 {
+    extern __shared__ __align__(16) unsigned char rs_smem[];
     const ResizeItem it = items[blockIdx.x];
     if (it.frame >= fs.nframes) return;
     const uint8_t* __restrict__ base = fs.base[it.frame];
     const int bpitch = fs.pitch[it.frame];
     const LevelDesc& L = levels[it.level];
-    const int x = it.x0 + (threadIdx.x & 31);
-    const int y0 = it.y0 + (threadIdx.x >> 5) * kC4RowsPerWarp;
-    const int w = L.w, h = L.h;
-    if (x >= w || y0 >= h) return;
-    const int y1 = min(y0 + kC4RowsPerWarp, h);
-    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y0 * L.pitch + 4 * x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int w = L.w, h = L.h, rs = L.rs_rows;
+    const int R = rs > 0 ? rs : (rs < 0 ? -rs : kRsDirectRows);
+    const int y0 = it.y0 + warp * R;
+    if (y0 >= h) return;                                     // the whole warp
+    const int nrows = min(R, h - y0);
+    const int xa = it.x0 + lane, xb = xa + 32;
+    const bool va = xa < w, vb = xb < w;
     const int dpitch = L.pitch;
+    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y0 * dpitch + 4 * xa;
+
     if (L.mode == 2) {          // exact half: 2x2 box average (resize.cpp:2542-2578)
-        for (int y = y0; y < y1; y++, dst += dpitch) {
-            const uint2 a = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y) * bpitch) + x);
-            const uint2 b = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y + 1) * bpitch) + x);
-            unsigned o = 0;
+        for (int k = 0; k < nrows; k++, dst += dpitch) {
+            const int y = y0 + k;
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
-                const unsigned sum = ((a.x >> (8 * c)) & 255u) + ((a.y >> (8 * c)) & 255u) +
-                                     ((b.x >> (8 * c)) & 255u) + ((b.y >> (8 * c)) & 255u) + 2u;
-                o |= (sum >> 2) << (8 * c);
+            for (int c = 0; c < 2; c++) {
+                const int x = xa + 32 * c;
+                if (x >= w) continue;
+                const uint2 a = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y) * bpitch) + x);
+                const uint2 b = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y + 1) * bpitch) + x);
+                unsigned o = 0;
+#pragma unroll
+                for (int ch = 0; ch < 4; ch++) {
+                    const unsigned sum = ((a.x >> (8 * ch)) & 255u) + ((a.y >> (8 * ch)) & 255u) +
+                                         ((b.x >> (8 * ch)) & 255u) + ((b.y >> (8 * ch)) & 255u) + 2u;
+                    o |= (sum >> 2) << (8 * ch);
+                }
+                *reinterpret_cast<unsigned*>(dst + 128 * c) = o;
             }
-            *reinterpret_cast<unsigned*>(dst) = o;
         }
         return;
     }
-    const ResizeCoef cx = xtab[L.xtab_off + x];
-    const int sx0 = cx.s0, sx1 = cx.s1;
-    const unsigned a01 = cx.c0;
-    const ResizeCoef* __restrict__ yt = ytab + L.ytab_off;
-    // Horizontal results of two source rows live in A and B.  `r1` is the source row of the one that served as the
-    // LOWER tap of the previous destination row; when the next row's upper tap is that row, only one new source row
-    // is needed and the two buffers swap roles (par) instead of being copied.  The row index is the same for the
-    // whole warp, so none of these branches diverges.
-    HRow A, B;
+    const ResizeCoef* __restrict__ xt = xtab + L.xtab_off;
+    const ResizeCoef* __restrict__ yt = ytab + L.ytab_off + y0;
+    const ResizeCoef cxa = xt[min(xa, w - 1)], cxb = xt[min(xb, w - 1)];
+    if (rs == 0) {              // unstaged: a level so coarse that one row pair of the tile exceeds the slice
+        for (int k = 0; k < nrows; k++, dst += dpitch) {
+            const ResizeCoef cy = yt[k];
+            if (va) *reinterpret_cast<unsigned*>(dst) = direct_px(base, bpitch, cxa, cy);
+            if (vb) *reinterpret_cast<unsigned*>(dst + 128) = direct_px(base, bpitch, cxb, cy);
+        }
+        return;
+    }
+
+    // ---- stage the source rows of this warp
+    const unsigned ws = (unsigned)__cvta_generic_to_shared(rs_smem) + warp * kRsWarpStride;
+    const unsigned mbar = ws, ycoef = ws + 16, tile = ws + kRsHeader;
+    const int c_lo = xt[it.x0].s0 & ~3;                                   // first staged source column
+    int span = (xt[min(it.x0 + kRsTileW, w) - 1].s0 + 2 - c_lo + 3) & ~3; // through the second tap of the last column
+    span = min(span, ((bw + 3) & ~3) - c_lo);                              // rows are readable up to the next multiple of 4
+    const unsigned rowbytes = 4u * span;
+    ResizeCoef cyl = yt[min(lane, nrows - 1)];
+    const int r_lo = __shfl_sync(0xffffffffu, cyl.s0, 0);
+    const int r_hi = __shfl_sync(0xffffffffu, cyl.s1, nrows - 1);
+    const int nstaged = rs > 0 ? r_hi - r_lo + 1 : 2 * nrows;
+    const unsigned off0 = rs > 0 ? (cyl.s0 - r_lo) * rowbytes : 2 * lane * rowbytes;
+    const unsigned off1 = rs > 0 ? (cyl.s1 - r_lo) * rowbytes : off0 + rowbytes;
+    if (lane < nrows)
+        asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(ycoef + 16 * lane), "r"(off0), "r"(off1), "r"(cyl.c0), "r"(cyl.c1) : "memory");
+    if (lane == 0) mbar_init(mbar, 1);
+    __syncwarp();
+    if (lane == 0) mbar_expect_tx(mbar, nstaged * rowbytes);
+    const uint8_t* __restrict__ src0 = base + 4 * c_lo;
+    if (rs > 0) {
+        for (int j = lane; j < nstaged; j += 32) bulk_g2s(tile + j * rowbytes, src0 + (size_t)(r_lo + j) * bpitch, rowbytes, mbar);
+    } else if (lane < nrows) {
+        bulk_g2s(tile + off0, src0 + (size_t)cyl.s0 * bpitch, rowbytes, mbar);
+        bulk_g2s(tile + off1, src0 + (size_t)cyl.s1 * bpitch, rowbytes, mbar);
+    }
+    const unsigned cola = tile + 4 * (cxa.s0 - c_lo), colb = tile + 4 * (cxb.s0 - c_lo);
+    const unsigned a01a = cxa.c0, a01b = cxb.c0;
+    mbar_wait(mbar, 0);
+
+    // Horizontal results of two source rows live in A and B (per column).  `r1` is the staged offset of the row that
+    // served as the LOWER tap of the previous destination row; when the next row's upper tap is that row, only one
+    // new source row is needed and the two buffers swap roles (par) instead of being copied.  The offsets are the
+    // same for the whole warp, so none of these branches diverges.
+    HRow Aa, Ba, Ab, Bb;
 #pragma unroll
-    for (int c = 0; c < 4; c++) A.t[c] = B.t[c] = 0;
-    int r1 = -1;
+    for (int c = 0; c < 4; c++) Aa.t[c] = Ba.t[c] = Ab.t[c] = Bb.t[c] = 0;
+    unsigned r1 = 0xffffffffu;
     bool par = false;           // false: lower tap of the previous row is in B; true: in A
-    for (int y = y0; y < y1; y++, dst += dpitch) {
-        const ResizeCoef cy = yt[y];
-        const int sy0 = cy.s0, sy1 = cy.s1;
-        // vertical pass, resize.cpp:1594-1601: ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2 >> 2; both products are
-        // non-negative and below 2^31, so (b<<16) * t >> 32 is the same truncating shift
-        const unsigned b0 = cy.c0, b1 = cy.c1;
-        auto vertical = [&](const HRow& h0, const HRow& h1) {
-            unsigned v[4];
-#pragma unroll
-            for (int c = 0; c < 4; c++)
-                v[c] = (__umulhi(b0, (unsigned)h0.t[c]) + __umulhi(b1, (unsigned)h1.t[c]) + 2u) >> 2;
-            *reinterpret_cast<unsigned*>(dst) = v[0] + v[1] * 256u + v[2] * 65536u + v[3] * 16777216u;
-        };
-        const uint8_t* __restrict__ row1 = base + (size_t)sy1 * bpitch;
-        if (sy0 == r1) {
-            if (par) { B = hrow_c4(row1, sx0, sx1, a01); vertical(A, B); }
-            else     { A = hrow_c4(row1, sx0, sx1, a01); vertical(B, A); }
+    for (int k = 0; k < nrows; k++, dst += dpitch) {
+        unsigned o0, o1, b0, b1;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(o0), "=r"(o1), "=r"(b0), "=r"(b1) : "r"(ycoef + 16 * k));
+        unsigned outa, outb;
+        if (o0 == r1) {
+            if (par) {
+                Ba = hrow_smem(cola + o1, a01a); Bb = hrow_smem(colb + o1, a01b);
+                outa = vertical_pack(Aa, Ba, b0, b1); outb = vertical_pack(Ab, Bb, b0, b1);
+            } else {
+                Aa = hrow_smem(cola + o1, a01a); Ab = hrow_smem(colb + o1, a01b);
+                outa = vertical_pack(Ba, Aa, b0, b1); outb = vertical_pack(Bb, Ab, b0, b1);
+            }
             par = !par;
         } else {
-            A = hrow_c4(base + (size_t)sy0 * bpitch, sx0, sx1, a01);
-            B = hrow_c4(row1, sx0, sx1, a01);
-            vertical(A, B);
+            Aa = hrow_smem(cola + o0, a01a); Ab = hrow_smem(colb + o0, a01b);
+            Ba = hrow_smem(cola + o1, a01a); Bb = hrow_smem(colb + o1, a01b);
+            outa = vertical_pack(Aa, Ba, b0, b1); outb = vertical_pack(Ab, Bb, b0, b1);
             par = false;
         }
-        r1 = sy1;
+        r1 = o1;
+        if (va) *reinterpret_cast<unsigned*>(dst) = outa;
+        if (vb) *reinterpret_cast<unsigned*>(dst + 128) = outb;
     }
 }
 
@@ -167,8 +281,36 @@ resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
 
 }  // namespace
 
-int resize_tile_w(int cn) { return cn == 4 ? kC4TileW : 128; }
-int resize_tile_h(int cn) { return cn == 4 ? kC4TileH : 8; }
+int resize_tile_w(int cn) { return cn == 4 ? kRsTileW : 128; }
+int resize_tile_h(int cn, int rs_rows)
+{
+    if (cn != 4) return 8;
+    return kRsWarps * (rs_rows > 0 ? rs_rows : (rs_rows < 0 ? -rs_rows : kRsDirectRows));
+}
+
+// Destination rows per warp for one 8UC4 level, from the level's own coefficient tables: the largest R whose
+// staged source slice fits kRsWarpBytes for every warp tile.  > 0: the rows [s0(first), s1(last)] are staged as
+// one range; < 0: only the two source rows of every destination row (cheaper from scale 2 up); 0: no staging.
+int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w)
+{
+    int span = 0;
+    for (int x0 = 0; x0 < dst_w; x0 += kRsTileW) {
+        const int c_lo = xt[x0].s0 & ~3;
+        int sp = (xt[std::min(x0 + kRsTileW, dst_w) - 1].s0 + 2 - c_lo + 3) & ~3;
+        sp = std::min(sp, ((src_w + 3) & ~3) - c_lo);
+        span = std::max(span, sp);
+    }
+    const int rowbytes = 4 * span, slack = 16;      // the second tap of the last column may lie one pixel past the span
+    for (int R = kRsMaxRows; R >= 1; R >>= 1) {
+        int range = 0;
+        for (int y0 = 0; y0 < dst_h; y0 += R)
+            range = std::max(range, yt[std::min(y0 + R, dst_h) - 1].s1 - yt[y0].s0 + 1);
+        const int pairs = 2 * R;
+        if (range <= pairs && range * rowbytes + slack <= kRsWarpBytes) return R;
+        if (pairs < range && pairs * rowbytes + slack <= kRsWarpBytes) return -R;
+    }
+    return 0;
+}
 
 void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
@@ -176,7 +318,7 @@ void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
 {
     if (nitems <= 0) return;
     if (cn == 4)
-        resize_c4_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+        resize_c4_kernel<<<nitems, kRsWarps * 32, kRsWarps * kRsWarpStride + 16, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
     else
         resize_c1_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
 }

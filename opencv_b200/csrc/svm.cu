@@ -24,10 +24,12 @@ namespace {
 
 constexpr int kSvmWarps = 9;                 // one per float4 of a block histogram
 constexpr int kSvmThreads = kSvmWarps * 32;
-constexpr int kT = 8;                        // adjacent windows per thread
-constexpr int kTileWX = 4 * kT;              // 32
-constexpr int kTileWY = 8;
-constexpr int kRing = kTileWY + 1;           // rows resident: 8 in use + 1 in flight
+constexpr int kT = 16;                       // adjacent windows per thread
+constexpr int kXG = 2;                       // groups of kT windows across a warp
+constexpr int kLY = 32 / kXG;                // window rows across a warp
+constexpr int kTileWX = kXG * kT;            // 32
+constexpr int kTileWY = kLY;                 // 16
+constexpr int kRing = kTileWY + 1;           // rows resident: 16 in use + 1 in flight
 constexpr int kMaxWBX = 7;
 constexpr int kRowBlocks = kTileWX + kMaxWBX - 1;          // 38
 // a ring slot is 11 x 128 B; block row `by_abs` is stored at float offset 4 * (by_abs & 7) inside its slot, so the
@@ -38,7 +40,7 @@ constexpr int kMaxCoef = 7 * 15 * kHist;                   // 3780
 constexpr int kRedStride = kTileWX + 1;
 
 struct SvmSmem {
-    float ring[kRing][kRowFloats];           // 49,392 B
+    float ring[kRing][kRowFloats];           // 95,744 B
     float coef[kMaxCoef];                    // 15,120 B
 };
 
@@ -77,14 +79,14 @@ __device__ __forceinline__ void load_row(float* dst, const float* __restrict__ p
 }
 
 template <int WBX>
-__global__ void __launch_bounds__(kSvmThreads, 3)
+__global__ void __launch_bounds__(kSvmThreads, 2)
 svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
            const float* __restrict__ hist, const __grid_constant__ SvmParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SvmSmem& s = *reinterpret_cast<SvmSmem*>(smem_raw);
     const int tid = threadIdx.x, q = tid >> 5, lane = tid & 31;
-    const int ly = lane & 7, xg = lane >> 3;
+    const int ly = lane % kLY, xg = lane / kLY;
 
     const SvmItem it = items[blockIdx.x];
     if (it.frame >= fs.nframes) return;
@@ -109,7 +111,7 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
 
         for (int by = 0; by < P.win_by; by++) {
             cp_async_wait_all();
-            __syncthreads();                                   // rows by .. by+7 are resident; slot of row by-1 is free
+            __syncthreads();                                   // rows by .. by+15 are resident; slot of row by-1 is free
             if (by + 1 < P.win_by) {                           // prefetch the row the next step adds
                 load_row(s.ring[(by + kTileWY) % kRing], plane, nbx, nby, wy0 + by + kTileWY, wx0, tid);
                 cp_async_commit();
@@ -134,12 +136,12 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
         }
         // ---- reduce the 9 k-partials through shared memory (aliases the ring)
         __syncthreads();
-        float* red = &s.ring[0][0];                            // [9][8][33]: odd row stride, the 8 window rows of a store hit 8 banks
+        float* red = &s.ring[0][0];                            // [9][16][33]: odd row stride, the window rows of a store hit different banks
 #pragma unroll
         for (int j = 0; j < kT; j++) red[(q * kTileWY + ly) * kRedStride + xg * kT + j] = acc[j].x + acc[j].y;
         __syncthreads();
-        if (tid < kTileWY * kTileWX) {
-            const int wy_l = tid >> 5, wx_l = tid & 31;
+        for (int w = tid; w < kTileWY * kTileWX; w += kSvmThreads) {      // whole warps: 512 = 288 + 7 * 32
+            const int wy_l = w / kTileWX, wx_l = w % kTileWX;
             float sc = 0.f;
 #pragma unroll
             for (int k = 0; k < kSvmWarps; k++) sc += red[(k * kTileWY + wy_l) * kRedStride + wx_l];
