@@ -423,7 +423,7 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
         sp.cand = reinterpret_cast<Candidate*>(h->d_cand.p + 16);
         sp.cand_count = reinterpret_cast<unsigned int*>(h->d_cand.p);
         sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
-        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, st);
+        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, h->num_sms, st);
         (*launches)++;
     }
     if (h->timing) cudaEventRecord(h->ev[4], st);

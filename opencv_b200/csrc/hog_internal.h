@@ -97,7 +97,7 @@ struct SvmParams {
     int tag;                   // OR-ed into Candidate::level: frame-in-chunk << 20 (detector goes to bits 16..19)
 };
 void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
-                const SvmParams& p, cudaStream_t st);
+                const SvmParams& p, int num_sms, cudaStream_t st);
 int svm_tile_wx();   // tile geometry the host uses to build SvmItems
 int svm_tile_wy();
 

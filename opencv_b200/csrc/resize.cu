@@ -34,11 +34,17 @@ __device__ __forceinline__ int vlin(int h0, int h1, int b0, int b1)
 //     pyramid's pixels); both taps of a channel are one IDP.2A (16-bit weights x 8-bit samples).
 //   * Vertical pass + pack: the two truncated products of channels c and c+2 are packed by IMADs into 16-bit
 //     fields, rounded and shifted together, and one PRMT assembles the four bytes.
-constexpr int kRsWarps = 4;
+#ifndef HOGB200_RS_WARPS
+#define HOGB200_RS_WARPS 4
+#endif
+#ifndef HOGB200_RS_BYTES
+#define HOGB200_RS_BYTES 6144
+#endif
+constexpr int kRsWarps = HOGB200_RS_WARPS;
 constexpr int kRsTileW = 64;
 constexpr int kRsMaxRows = 16;                              // destination rows per warp, at most
 constexpr int kRsHeader = 16 + 16 * kRsMaxRows;             // mbarrier + per-row coefficients
-constexpr int kRsWarpBytes = 6144;                          // staged source pixels per warp
+constexpr int kRsWarpBytes = HOGB200_RS_BYTES;                        // staged source pixels per warp
 constexpr int kRsWarpStride = kRsHeader + kRsWarpBytes;
 constexpr int kRsDirectRows = 8;                            // rows per warp of the unstaged paths
 
@@ -317,8 +323,11 @@ void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const ResizeItem* d_items, int nitems, cudaStream_t st)
 {
     if (nitems <= 0) return;
-    if (cn == 4)
-        resize_c4_kernel<<<nitems, kRsWarps * 32, kRsWarps * kRsWarpStride + 16, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+    if (cn == 4) {
+        constexpr int smem = kRsWarps * kRsWarpStride + 16;
+        if (smem > 48 * 1024) cudaFuncSetAttribute(resize_c4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        resize_c4_kernel<<<nitems, kRsWarps * 32, smem, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+    }
     else
         resize_c1_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
 }

@@ -17,13 +17,17 @@
 //     and windows with score >= hit_threshold are appended to a global candidate list (ballot + one atomic per
 //     warp).  The host sorts the (tiny) list into the reference's row-major order.
 #include "hog_internal.h"
+#include <algorithm>
 
 namespace hogk {
 
 namespace {
 
-constexpr int kSvmWarps = 9;                 // one per float4 of a block histogram
-constexpr int kSvmThreads = kSvmWarps * 32;
+constexpr int kSvmWarps = 9;                 // consumer warps of a group: one per float4 of a block histogram
+constexpr int kGroups = 2;                   // independent consumer groups per CTA (each with its own ring and producer)
+constexpr int kGroupThreads = kSvmWarps * 32;
+constexpr int kConsumerThreads = kGroups * kGroupThreads;                 // 576
+constexpr int kSvmThreads = kConsumerThreads + kGroups * 32;              // + one producer warp per group = 640
 constexpr int kT = 16;                       // adjacent windows per thread
 constexpr int kXG = 2;                       // groups of kT windows across a warp
 constexpr int kLY = 32 / kXG;                // window rows across a warp
@@ -37,18 +41,21 @@ constexpr int kRowBlocks = kTileWX + kMaxWBX - 1;          // 38
 constexpr int kRowFloats = 1408;
 static_assert(kRowBlocks * kHist + 28 <= kRowFloats, "ring slot too small");
 constexpr int kMaxCoef = 7 * 15 * kHist;                   // 3780
-constexpr int kRedStride = kTileWX + 1;
+constexpr int kRedCols = kXG * (kT / 2);                   // windows per tile row in one reduction round (16)
+constexpr int kRedStride = kRedCols + 1;
 
-struct SvmSmem {
-    float ring[kRing][kRowFloats];           // 95,744 B
-    float coef[kMaxCoef];                    // 15,120 B
+struct GroupSmem {
+    float ring[kRing][kRowFloats];                         // 95,744 B
+    float red[kSvmWarps][kTileWY][kRedStride];             //  9,792 B: k-partials of half a tile
+    unsigned long long full[kRing], empty[kRing];          // mbarriers: row landed / row no longer read
 };
+struct SvmSmem {
+    float coef[kMaxCoef];                                  // 15,120 B, shared by both groups
+    float pad[4];
+    GroupSmem g[kGroups];
+};
+static_assert(sizeof(SvmSmem) <= 227 * 1024, "shared memory");
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
-{
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem));
-}
 // packed FP32 (Blackwell FFMA2): d = a * b + c on both halves
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c)
 {
@@ -61,108 +68,196 @@ __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c)
     asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
     return d;
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
-// Load block row `by_abs` (blocks wx0 .. wx0+kRowBlocks) of the level's histogram plane into a ring slot;
-// out-of-range blocks / rows are zero-filled.
-__device__ __forceinline__ void load_row(float* dst, const float* __restrict__ plane, int nbx, int nby,
-                                         int by_abs, int bx0, int tid)
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count)
 {
-    const int nvalid = (by_abs < nby) ? max(0, min(kRowBlocks, nbx - bx0)) * (kHist / 4) : 0;   // float4 chunks
-    const float4* src = reinterpret_cast<const float4*>(plane + ((long long)by_abs * nbx + bx0) * kHist);
-    dst += 4 * (by_abs & 7);
-    for (int i = tid; i < kRowBlocks * (kHist / 4); i += kSvmThreads) {
-        if (i < nvalid) cp_async16(dst + 4 * i, src + i);
-        else *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(unsigned mbar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned mbar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(mbar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void group_sync(int g)      // the 9 consumer warps of group g
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(kGroupThreads) : "memory");
 }
 
+// Persistent kernel, one CTA per SM.  Each of the two consumer groups walks its own list of window tiles; its
+// producer warp (one elected lane) streams the block rows of those tiles, tile after tile, through the group's ring
+// with one bulk async copy per row, so the first rows of the next tile land while the current one is still being
+// scored and no consumer warp ever waits for a CTA-wide barrier inside a tile:
+//   full[slot]   producer -> consumers: the row's bytes have landed (expect_tx / complete_tx)
+//   empty[slot]  consumers -> producer: all 9 warps are past the last step that reads the row
+// `n` numbers the rows a group has pushed through its ring since the kernel started; slot = n % kRing and the
+// mbarrier phase parity is (n / kRing) & 1 on both sides.
 template <int WBX>
-__global__ void __launch_bounds__(kSvmThreads, 2)
+__global__ void __launch_bounds__(kSvmThreads, 1)
 svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
-           const float* __restrict__ hist, const __grid_constant__ SvmParams P)
+           int nitems, const float* __restrict__ hist, const __grid_constant__ SvmParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SvmSmem& s = *reinterpret_cast<SvmSmem*>(smem_raw);
-    const int tid = threadIdx.x, q = tid >> 5, lane = tid & 31;
-    const int ly = lane % kLY, xg = lane / kLY;
-
-    const SvmItem it = items[blockIdx.x];
-    if (it.frame >= fs.nframes) return;
-    const LevelDesc& L = levels[it.level];
-    const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
-    const int nbx = L.nbx, nby = L.nby;
-    // dense (stride-1) window grid of the level; the requested stride subsamples it at output time
-    const int vwx = nbx - WBX + 1, vwy = nby - P.win_by + 1;
-    const int wx0 = it.wx0, wy0 = it.wy0;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool producer = tid >= kConsumerThreads;
+    const int g = producer ? (tid - kConsumerThreads) >> 5 : tid / kGroupThreads;
+    GroupSmem& G = s.g[g];
+    const unsigned full0 = smem_u32(&G.full[0]), empty0 = smem_u32(&G.empty[0]);
+    if (tid == 0) {
+        for (int gg = 0; gg < kGroups; gg++)
+            for (int i = 0; i < kRing; i++) {
+                mbar_init(smem_u32(&s.g[gg].full[i]), 1);
+                mbar_init(smem_u32(&s.g[gg].empty[i]), kSvmWarps);
+            }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     const int ncoef = P.win_by * WBX * kHist;
+    const int tile_rows = kTileWY + P.win_by - 1;
+    const int gid = blockIdx.x * kGroups + g, gstride = gridDim.x * kGroups;
+    unsigned n = 0;
 
     for (int d = 0; d < P.ndet; d++) {
-        __syncthreads();     // previous detector's reduction reads are done
+        __syncthreads();     // barriers initialised / every group is done with the previous detector
         for (int i = tid; i < ncoef / 4; i += kSvmThreads)
             reinterpret_cast<float4*>(s.coef)[i] = __ldg(reinterpret_cast<const float4*>(P.det[d]) + i);
-        for (int r = 0; r < kTileWY; r++) load_row(s.ring[r], plane, nbx, nby, wy0 + r, wx0, tid);
-        cp_async_commit();
+        __syncthreads();
 
-        float2 acc[kT];         // (even k, odd k) partial sums: two packed FFMA2 per float4 pair
-#pragma unroll
-        for (int j = 0; j < kT; j++) acc[j] = make_float2(0.f, 0.f);
-
-        for (int by = 0; by < P.win_by; by++) {
-            cp_async_wait_all();
-            __syncthreads();                                   // rows by .. by+15 are resident; slot of row by-1 is free
-            if (by + 1 < P.win_by) {                           // prefetch the row the next step adds
-                load_row(s.ring[(by + kTileWY) % kRing], plane, nbx, nby, wy0 + by + kTileWY, wx0, tid);
-                cp_async_commit();
-            }
-            float4 wv[WBX];
-#pragma unroll
-            for (int bx = 0; bx < WBX; bx++)
-                wv[bx] = *reinterpret_cast<const float4*>(&s.coef[(by * WBX + bx) * kHist + 4 * q]);
-            const float* rowp = &s.ring[(by + ly) % kRing][4 * ((wy0 + by + ly) & 7) + xg * kT * kHist + 4 * q];
-#pragma unroll
-            for (int X = 0; X < kT + WBX - 1; X++) {
-                const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist);
-#pragma unroll
-                for (int bx = 0; bx < WBX; bx++) {
-                    const int j = X - bx;
-                    if (j >= 0 && j < kT) {
-                        acc[j] = fma2(make_float2(hv.x, hv.y), make_float2(wv[bx].x, wv[bx].y), acc[j]);
-                        acc[j] = fma2(make_float2(hv.z, hv.w), make_float2(wv[bx].z, wv[bx].w), acc[j]);
+        if (producer) {
+            if (lane == 0) {
+                for (int ii = gid; ii < nitems; ii += gstride) {
+                    const SvmItem it = items[ii];
+                    if (it.frame >= fs.nframes) continue;
+                    const LevelDesc& L = levels[it.level];
+                    const int nbx = L.nbx, nby = L.nby;
+                    const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
+                    const unsigned bytes = (unsigned)max(0, min(kRowBlocks, nbx - it.wx0)) * (kHist * 4);
+                    const unsigned ring0 = smem_u32(&G.ring[0][0]);
+                    for (int r = 0; r < tile_rows; r++, n++) {
+                        const unsigned slot = n % kRing, use = n / kRing;
+                        if (use > 0) mbar_wait(empty0 + 8 * slot, (use - 1) & 1);
+                        const int by_abs = it.wy0 + r;
+                        if (by_abs < nby && bytes > 0) {         // rows below the level feed only windows that are discarded
+                            mbar_expect_tx(full0 + 8 * slot, bytes);
+                            bulk_g2s(ring0 + slot * (kRowFloats * 4) + 16 * (by_abs & 7),
+                                     plane + ((long long)by_abs * nbx + it.wx0) * kHist, bytes, full0 + 8 * slot);
+                        } else {
+                            mbar_arrive(full0 + 8 * slot);
+                        }
                     }
                 }
             }
+            __syncwarp();
+            continue;
         }
-        // ---- reduce the 9 k-partials through shared memory (aliases the ring)
-        __syncthreads();
-        float* red = &s.ring[0][0];                            // [9][16][33]: odd row stride, the window rows of a store hit different banks
+
+        // ---- consumers
+        const int gt = tid - g * kGroupThreads, q = gt >> 5;
+        const int ly = lane % kLY, xg = lane / kLY;
+        for (int ii = gid; ii < nitems; ii += gstride) {
+            const SvmItem it = items[ii];
+            if (it.frame >= fs.nframes) continue;
+            const LevelDesc& L = levels[it.level];
+            const int vwx = L.nbx - WBX + 1, vwy = L.nby - P.win_by + 1;   // dense (stride-1) window grid of the level
+            const int wx0 = it.wx0, wy0 = it.wy0;
+
+            float2 acc[kT];         // (even k, odd k) partial sums: two packed FFMA2 per float4 pair
 #pragma unroll
-        for (int j = 0; j < kT; j++) red[(q * kTileWY + ly) * kRedStride + xg * kT + j] = acc[j].x + acc[j].y;
-        __syncthreads();
-        for (int w = tid; w < kTileWY * kTileWX; w += kSvmThreads) {      // whole warps: 512 = 288 + 7 * 32
-            const int wy_l = w / kTileWX, wx_l = w % kTileWX;
-            float sc = 0.f;
+            for (int j = 0; j < kT; j++) acc[j] = make_float2(0.f, 0.f);
+            unsigned slot_l = (n + ly) % kRing;
+            if (lane < kTileWY) {                                   // the tile's first 16 rows, one lane each
+                const unsigned m = n + lane;
+                mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
+            }
+            __syncwarp();
+            for (int by = 0; by < P.win_by; by++) {
+                if (by > 0) {                                       // the row this step adds
+                    const unsigned m = n + by + kTileWY - 1;
+                    mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
+                }
+                float4 wv[WBX];
 #pragma unroll
-            for (int k = 0; k < kSvmWarps; k++) sc += red[(k * kTileWY + wy_l) * kRedStride + wx_l];
-            sc += P.bias[d];
-            const int vx = wx0 + wx_l, vy = wy0 + wy_l;
-            bool valid = vx < vwx && vy < vwy && (vx % P.stride_bx == 0) && (vy % P.stride_by == 0);
-            const int ox = vx / P.stride_bx, oy = vy / P.stride_by;
-            if (valid && P.scores) P.scores[d * P.score_plane + L.score_off + (long long)oy * L.nwx + ox] = sc;
-            const bool hit = valid && sc >= P.thresh;
-            const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (m) {
-                unsigned base = 0;
-                if (lane == 0) base = atomicAdd(P.cand_count, __popc(m));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (hit) {
-                    const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
-                    if (pos < P.cand_cap) {
-                        Candidate c; c.level = it.level | (d << 16) | (P.tag + (it.frame << 20)); c.x = ox; c.y = oy; c.score = sc;
-                        P.cand[pos] = c;
+                for (int bx = 0; bx < WBX; bx++)
+                    wv[bx] = *reinterpret_cast<const float4*>(&s.coef[(by * WBX + bx) * kHist + 4 * q]);
+                const float* rowp = &G.ring[slot_l][4 * ((wy0 + by + ly) & 7) + xg * kT * kHist + 4 * q];
+#pragma unroll
+                for (int X = 0; X < kT + WBX - 1; X++) {
+#if defined(SVM_EXP_NOLDS)
+                    const float4 hv = *reinterpret_cast<const float4*>(rowp + (X & 1) * kHist);
+#else
+                    const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist);
+#endif
+#pragma unroll
+                    for (int bx = 0; bx < WBX; bx++) {
+                        const int j = X - bx;
+#if defined(SVM_EXP_NOFMA)
+                        if (j >= 0 && j < kT && bx == 0) {
+#else
+                        if (j >= 0 && j < kT) {
+#endif
+                            acc[j] = fma2(make_float2(hv.x, hv.y), make_float2(wv[bx].x, wv[bx].y), acc[j]);
+                            acc[j] = fma2(make_float2(hv.z, hv.w), make_float2(wv[bx].z, wv[bx].w), acc[j]);
+                        }
                     }
                 }
+                __syncwarp();                                       // lanes 0 and 16 have read row n + by for the last time
+                if (lane == 0) mbar_arrive(empty0 + 8 * ((n + by) % kRing));
+                slot_l = slot_l + 1 == kRing ? 0 : slot_l + 1;
+            }
+            if (lane < kTileWY - 1) mbar_arrive(empty0 + 8 * ((n + P.win_by + lane) % kRing));   // the tile's last 15 rows
+            n += tile_rows;
+
+            // ---- sum the 9 k-partials through shared memory, half a tile (8 of a thread's 16 windows) per round
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+#pragma unroll
+                for (int jj = 0; jj < kT / 2; jj++)
+                    G.red[q][ly][xg * (kT / 2) + jj] = acc[r * (kT / 2) + jj].x + acc[r * (kT / 2) + jj].y;
+                group_sync(g);
+                if (gt < kTileWY * kRedCols) {                      // 256 threads = 8 whole warps
+                    const int wy_l = gt / kRedCols, c = gt % kRedCols;
+                    const int wx_l = (c / (kT / 2)) * kT + r * (kT / 2) + c % (kT / 2);
+                    float sc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < kSvmWarps; k++) sc += G.red[k][wy_l][c];
+                    sc += P.bias[d];
+                    const int vx = wx0 + wx_l, vy = wy0 + wy_l;
+                    const bool valid = vx < vwx && vy < vwy && (vx % P.stride_bx == 0) && (vy % P.stride_by == 0);
+                    const int ox = vx / P.stride_bx, oy = vy / P.stride_by;
+                    if (valid && P.scores) P.scores[d * P.score_plane + L.score_off + (long long)oy * L.nwx + ox] = sc;
+                    const bool hit = valid && sc >= P.thresh;
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (m) {
+                        unsigned base = 0;
+                        if (lane == 0) base = atomicAdd(P.cand_count, __popc(m));
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        if (hit) {
+                            const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
+                            if (pos < P.cand_cap) {
+                                Candidate c2; c2.level = it.level | (d << 16) | (P.tag + (it.frame << 20)); c2.x = ox; c2.y = oy; c2.score = sc;
+                                P.cand[pos] = c2;
+                            }
+                        }
+                    }
+                }
+                group_sync(g);
             }
         }
     }
@@ -194,15 +289,16 @@ int svm_tile_wx() { return kTileWX; }
 int svm_tile_wy() { return kTileWY; }
 
 void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
-                const SvmParams& p, cudaStream_t st)
+                const SvmParams& p, int num_sms, cudaStream_t st)
 {
     if (nitems <= 0 || p.ndet <= 0) return;
+    const int grid = std::max(1, std::min(num_sms, (nitems + kGroups - 1) / kGroups));
     if (p.win_bx == 7) {
         cudaFuncSetAttribute(svm_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<7><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, d_hist, p);
+        svm_kernel<7><<<grid, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, nitems, d_hist, p);
     } else if (p.win_bx == 5) {
         cudaFuncSetAttribute(svm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<5><<<nitems, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, d_hist, p);
+        svm_kernel<5><<<grid, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, nitems, d_hist, p);
     }
 }
 
