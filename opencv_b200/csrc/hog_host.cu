@@ -260,6 +260,7 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     size_t pyr = 0;
     std::vector<ResizeCoef> xtab, ytab;
     std::vector<ResizeItem> ritems; std::vector<HistItem> hitems; std::vector<SvmItem> sitems;
+    std::vector<int> scost;
     std::vector<LevelDesc> descs;
     for (size_t i = 0; i < scales.size(); i++) {
         LevelHost L;
@@ -295,7 +296,10 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
         const int vwx = L.nbx - wbx + 1, vwy = L.nby - wby + 1;
         if (L.nwx > 0 && vwx > 0 && vwy > 0)
             for (int wy = 0; wy < vwy; wy += svm_tile_wy())
-                for (int wx = 0; wx < vwx; wx += svm_tile_wx()) sitems.push_back(SvmItem{(short)i, (short)wx, (short)wy, 0});
+                for (int wx = 0; wx < vwx; wx += svm_tile_wx()) {
+                    sitems.push_back(SvmItem{(short)i, (short)wx, (short)wy, 0});
+                    scost.push_back(svm_tile_cost(vwx - wx, vwy - wy));
+                }
         P.lv.push_back(L); descs.push_back(D);
     }
     (void)sbx; (void)sby;
@@ -312,6 +316,16 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     std::stable_sort(hitems.begin(), hitems.end(), [](const HistItem& a, const HistItem& b) {
         return a.nby > b.nby;       // a partial tile costs a warp as much as a full one
     });
+    // SVM tiles are dealt round-robin to the persistent CTAs: most expensive first, so that the partly filled edge
+    // tiles even out the tail
+    {
+        std::vector<int> order(sitems.size());
+        for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return scost[a] > scost[b]; });
+        std::vector<SvmItem> sorted; sorted.reserve(sitems.size());
+        for (int i : order) sorted.push_back(sitems[i]);
+        sitems.swap(sorted);
+    }
     // replicate the lists for frames 1 .. group-1 (frame-minor, so that equal-sized items of all frames are adjacent)
     if (group > 1) {
         std::vector<ResizeItem> r2; std::vector<HistItem> h2; std::vector<SvmItem> s2;

@@ -100,6 +100,7 @@ void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_
                 const SvmParams& p, int num_sms, cudaStream_t st);
 int svm_tile_wx();   // tile geometry the host uses to build SvmItems
 int svm_tile_wy();
+int svm_tile_cost(int cols_left, int rows_left);   // relative time of a tile with that many valid windows right / below its origin
 
 void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_hist, int win_bx, int win_by,
                     int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);

@@ -93,6 +93,18 @@ __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(mbar), "r"(parity) : "memory");
 }
+__device__ __forceinline__ bool mbar_test(unsigned mbar, unsigned parity)      // non-blocking
+{
+    unsigned ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// slot / parity one position before (nslot, npar)
+__device__ __forceinline__ unsigned nslot_prev(unsigned nslot) { return nslot == 0 ? kRing - 1 : nslot - 1; }
+__device__ __forceinline__ unsigned npar_prev(unsigned nslot, unsigned npar) { return nslot == 0 ? npar ^ 1 : npar; }
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned mbar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -254,11 +266,14 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
             for (int j = 0; j < kT; j++) accA[j] = accB[j] = make_float2(0.f, 0.f);
             exA[0] = exA[1] = exB[0] = exB[1] = make_float2(0.f, 0.f);
             unsigned slot_l = (pos0 + 2 * pr) % kRing;
+            unsigned oslot = pos0 % kRing;                               // slot of the band's oldest live row
+            unsigned nslot = (pos0 + kBandRows - 1) % kRing;             // slot / parity of the row the NEXT step adds
+            unsigned npar = ((pos0 + kBandRows - 1) / kRing) & 1;
+            bool ready = true;
             for (int t = 0; t <= win_by; t++) {
-                if (t > 0) {                                            // the row this step adds
-                    const unsigned m = pos0 + t + kBandRows - 2;
-                    mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
-                }
+                if (!ready) mbar_wait(full0 + 8 * nslot_prev(nslot), npar_prev(nslot, npar));
+                // poll the next step's row now, so that the answer is there when this step's arithmetic is done
+                ready = t == win_by || mbar_test(full0 + 8 * nslot, npar);
                 const float* rowp = &s.ring[slot_l][cg * kT * kHist];
                 const float* ca = s.coef + t * (WBX * kHist);
                 const float* cb = ca - WBX * kHist;
@@ -266,8 +281,10 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
                 else if (t == win_by) svm_step<WBX, false, true>(accA, accB, exA, exB, ca, cb, rowp, q);
                 else svm_step<WBX, true, true>(accA, accB, exA, exB, ca, cb, rowp, q);
                 __syncwarp();                                           // every lane has read row pos0 + t for the last time
-                if (lane == 0) mbar_arrive(empty0 + 8 * ((pos0 + t) % kRing));
+                if (lane == 0) mbar_arrive(empty0 + 8 * oslot);
                 slot_l = slot_l + 1 == kRing ? 0 : slot_l + 1;
+                oslot = oslot + 1 == kRing ? 0 : oslot + 1;
+                if (++nslot == kRing) { nslot = 0; npar ^= 1; }
             }
             if (lane < kBandRows - 2) mbar_arrive(empty0 + 8 * ((pos0 + win_by + 1 + lane) % kRing));   // the band's last 6 rows
 
@@ -363,6 +380,18 @@ __global__ void extract_kernel(const LevelDesc* __restrict__ level, const float*
 
 int svm_tile_wx() { return kTileWX; }
 int svm_tile_wy() { return kTileWY; }
+int svm_tile_cost(int cols_left, int rows_left)
+{
+    // a warp = (band, column group) works only if its 8 x 16 windows intersect the level; the tile takes as long as
+    // the busiest sub-partition, which hosts (band s, group 0) and (band (s + 2) % 4, group 1)
+    const int nb = std::min(kBands, (rows_left + kBandRows - 1) / kBandRows), nc = cols_left > kT ? 2 : 1;
+    int busiest = 0, total = 0;
+    for (int sp = 0; sp < 4; sp++) {
+        const int a = (sp < nb) + (nc > 1 && ((sp + 2) & 3) < nb);
+        busiest = std::max(busiest, a); total += a;
+    }
+    return busiest * 16 + total;
+}
 
 void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
                 const SvmParams& p, int num_sms, cudaStream_t st)
