@@ -18,14 +18,14 @@
 //     DOWN the strip: vertical neighbours live in registers, lateral ones in the same thread or one shuffle away;
 //   * the block window weight is separable, w(i,j) = A_cy[i] * A_cx[j] (Gaussian x bilinear cell weight), so votes
 //     are first accumulated VERTICALLY into per-column, per-bin partial sums in shared memory (private per thread:
-//     no atomics, fixed order, bit-reproducible); each pixel feeds 3 live accumulators with one packed
-//     FFMA2 read-modify-write each: the (bin0: mag*(1-a), bin0+1: mag*a) pair is kept as a float2 indexed by bin0
-//     and the second half is folded into bin0+1 after the horizontal pass;
+//     no atomics, fixed order, bit-reproducible); each pixel feeds 3 live accumulator slots, two scalar
+//     read-modify-writes each (bin0 += mag*(1-a), bin0+1 += mag*a); a tenth accumulator row takes the second vote
+//     of bin 8 and is folded into bin 0 by the horizontal pass;
 //   * orientation binning is branch- and conversion-free: angle in bin units with its sign taken from
 //     sign(dx)^sign(dy), floor() by the 1.5*2^23 magic add, whose mantissa is at the same time the shared-memory
 //     row offset of the bin (no wrap needed: the 9 reachable rows are a cyclic rotation of the 9 bins);
-//   * every 4 rows one accumulator is complete; a HORIZONTAL pass (lane <-> (bin, cell)) contracts the 120 columns
-//     with the 12-tap horizontal weights into the four cell sums of 14 blocks (packed FFMA2 again);
+//   * every 4 rows one accumulator slot is complete; a HORIZONTAL pass (lane <-> (row, cell)) contracts the 120
+//     columns with the 24-tap horizontal weights into the four cell sums of 14 blocks;
 //   * once both cell rows of a block row are in, 4 lanes per block do L2-Hys with shuffle reductions; the 2016-byte
 //     block row leaves as coalesced 16-byte stores.
 #include "hog_internal.h"
