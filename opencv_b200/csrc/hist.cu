@@ -40,7 +40,7 @@ namespace {
 #define HOGB200_HIST_WARPS 12
 #endif
 #ifndef HOGB200_LUT_COPIES
-#define HOGB200_LUT_COPIES 8
+#define HOGB200_LUT_COPIES 16
 #endif
 constexpr int kWarps = HOGB200_HIST_WARPS;         // independent workers per CTA (one CTA per SM)
 constexpr int kThreads = kWarps * 32;
@@ -61,7 +61,7 @@ struct __align__(16) WarpSmem {
 };
 struct __align__(16) Smem {
     float4 wrow[8];                                //    128 B  vertical weights of row o of a cell row: (R, Q, P/T, -)
-    float lut[256 * kLutCopies];                   //  8,192 B  gamma LUT, lut[v*copies + lane%copies]
+    float lut[256 * kLutCopies];                   // 16,384 B  gamma LUT, lut[v*copies + lane%copies]
     WarpSmem w[kWarps];                            // 12 x 17,376 B
 };
 

@@ -201,17 +201,20 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
         __syncthreads();
 
         if (producer) {
-            if (lane == 0) {
-                const unsigned ring0 = smem_u32(&s.ring[0][0]);
-                for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
-                    const SvmItem it = items[ii];
-                    if (it.frame >= fs.nframes) continue;
-                    const LevelDesc& L = levels[it.level];
-                    const int nbx = L.nbx, nby = L.nby;
-                    const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
-                    const unsigned bytes = (unsigned)max(0, min(kRowBlocks, nbx - it.wx0)) * (kHist * 4);
-                    for (int r = 0; r < tile_rows; r++, n++) {
-                        const unsigned slot = n % kRing, use = n / kRing;
+            // every lane streams its own rows (lane, lane + 32 of each tile): the waits for free slots overlap, so the
+            // 30-odd rows that become loadable at once when a tile ends are issued back to back
+            const unsigned ring0 = smem_u32(&s.ring[0][0]);
+            for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
+                const SvmItem it = items[ii];
+                if (it.frame >= fs.nframes) continue;
+                const LevelDesc& L = levels[it.level];
+                const int nbx = L.nbx, nby = L.nby;
+                const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
+                const unsigned bytes = (unsigned)max(0, min(kRowBlocks, nbx - it.wx0)) * (kHist * 4);
+                for (int r0 = 0; r0 < tile_rows; r0 += 32) {
+                    const int r = r0 + lane;
+                    if (r < tile_rows) {
+                        const unsigned m = n + r, slot = m % kRing, use = m / kRing;
                         if (use > 0) mbar_wait(empty0 + 8 * slot, (use - 1) & 1);
                         const int by_abs = it.wy0 + r;
                         if (by_abs < nby && bytes > 0) {         // rows below the level feed only discarded windows
@@ -222,7 +225,11 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
                             mbar_arrive(full0 + 8 * slot);
                         }
                     }
+                    // lanes stay within 32 < kRing positions of each other: a parity wait on a slot is only sound
+                    // once the slot's previous use has been issued
+                    __syncwarp();
                 }
+                n += tile_rows;
             }
             __syncwarp();
             continue;
