@@ -118,6 +118,22 @@ __device__ __forceinline__ float2 fma2(float w, float2 b, float2 c)
     return d;
 }
 
+// packed FP32 add / sub / mul (round-to-nearest: same results as the scalar operations)
+__device__ __forceinline__ float2 pk_op2(int op, float2 a, float2 b)
+{
+    unsigned long long ra, rb, rd;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    if (op == 0)      asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    else if (op == 1) asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    else              asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    float2 d;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return pk_op2(1, a, b); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return pk_op2(2, a, b); }
+
 __device__ __forceinline__ float sqrt_approx(float x)
 {
     float r;
@@ -170,19 +186,30 @@ template <int NC>
 __device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], const float (&U)[3], const float (&D)[3],
                                       float xm)
 {
-    float dx = (R[0] - L[0]) * xm, dy = D[0] - U[0];
-    // unfused, like the CPU's SSE2 (dx*dx)+(dy*dy): channel selection is discontinuous, an FMA here would break
-    // exact ties such as (a,b) vs (b,a) differently from the reference
-    float m = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-#pragma unroll
-    for (int c = 1; c < NC; c++) {
-        const float ddx = (R[c] - L[c]) * xm, ddy = D[c] - U[c];
-        const float mm = __fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy));
+    float dx, dy, m;
+    if (NC == 3) {
+        // channels 0 and 1 as one packed operation each (same roundings as the scalar form), channel 2 scalar
+        const float2 xm2 = make_float2(xm, xm);
+        const float2 dx01 = mul2(sub2(make_float2(R[0], R[1]), make_float2(L[0], L[1])), xm2);
+        const float2 dy01 = sub2(make_float2(D[0], D[1]), make_float2(U[0], U[1]));
+        // unfused, like the CPU's SSE2 (dx*dx)+(dy*dy): channel selection is discontinuous, an FMA here would break
+        // exact ties such as (a,b) vs (b,a) differently from the reference.  The two sums stay scalar: ptxas
+        // contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 in spite of the .rn.
+        const float2 dxx = mul2(dx01, dx01), dyy = mul2(dy01, dy01);
+        const float mm0 = __fadd_rn(dxx.x, dyy.x), mm1 = __fadd_rn(dxx.y, dyy.y);
+        const float dx2 = (R[2] - L[2]) * xm, dy2 = D[2] - U[2];
+        const float mm2 = __fadd_rn(__fmul_rn(dx2, dx2), __fmul_rn(dy2, dy2));
         // strict >: the first channel in processing order wins ties (hog.cu:694-712, CPU SSE2 body hog.cpp:393-403);
         // the caller reverses the processing order in the last w%4 columns, where the CPU's scalar tail lets the
         // highest channel win (hog.cpp:455-477)
-        const bool p = mm > m;
-        dx = p ? ddx : dx; dy = p ? ddy : dy; m = fmaxf(m, mm);
+        dx = dx01.x; dy = dy01.x; m = mm0;
+        const bool p1 = mm1 > m;
+        dx = p1 ? dx01.y : dx; dy = p1 ? dy01.y : dy; m = fmaxf(m, mm1);
+        const bool p2 = mm2 > m;
+        dx = p2 ? dx2 : dx; dy = p2 ? dy2 : dy; m = fmaxf(m, mm2);
+    } else {
+        dx = (R[0] - L[0]) * xm; dy = D[0] - U[0];
+        m = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
     }
     const float mag = sqrt_approx(m);      // = sqrt(dx*dx + dy*dy) of the winning channel (magnitude32f)
     // fastAtan32f (core/src/mathfuncs_core.simd.hpp:45-71), in units of one bin (20 degrees): coefficients * 9/pi
