@@ -43,13 +43,16 @@ typedef struct hogb200_geom {
 } hogb200_geom;
 
 /* One frame: 8-bit, 1 or 4 interleaved channels (CV_8UC1 / CV_8UC4, hog.cpp:340,421,496), pitched rows.
+ * 3 channels (CV_8UC3, B,G,R) are accepted too and widened to B,G,R,255 on the device: the cvtColor that
+ * example_gpu_tbd runs on the host before its upload (samples/gpu/tbd.cpp:573-599); results equal those of the
+ * 8UC4 frame.  hogb200_resize takes 1 or 4 channels only.
  * `data` is a device pointer when on_device != 0 (a GpuMat), else a host pointer (pinned memory makes the
  * upload asynchronous).  A ROI is expressed by data/pitch as with GpuMat. */
 typedef struct hogb200_image {
     const void* data;
     size_t pitch;      /* bytes between rows */
     int width, height;
-    int channels;      /* 1 or 4 */
+    int channels;      /* 1, 3 or 4 */
     int on_device;
 } hogb200_image;
 

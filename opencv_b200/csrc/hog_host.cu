@@ -109,7 +109,7 @@ struct hogb200 {
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
     cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
     // workspace
-    DevBuf<uint8_t> d_frame[2 * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
+    DevBuf<uint8_t> d_frame[2 * kMaxGroup]; DevBuf<uint8_t> d_raw[2 * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
     DevBuf<unsigned int> d_queue;   // work-queue counters of the fused histogram kernel (self re-arming)
     int num_sms = 148;
     DevBuf<unsigned char> d_cand;   // [16-byte header: counter][Candidate * cap]
@@ -365,8 +365,10 @@ struct FrameRef { const uint8_t* dev; int pitch; };
 int check_image(const hogb200_image* img)
 {
     if (!img || !img->data) return fail(HOGB200_BAD_ARG, "image is null");
-    if (img->channels != 1 && img->channels != 4)
-        return fail(HOGB200_BAD_ARG, "image type must be CV_8UC1 or CV_8UC4 (cudaobjdetect/src/hog.cpp:340)");
+    // 8UC1 / 8UC4 as cv::cuda::HOG (cudaobjdetect/src/hog.cpp:340); 8UC3 (B,G,R) is widened to 8UC4 on the device,
+    // which is the cvtColor example_gpu_tbd runs on the host before its upload (samples/gpu/tbd.cpp:573-599)
+    if (img->channels != 1 && img->channels != 3 && img->channels != 4)
+        return fail(HOGB200_BAD_ARG, "image type must be CV_8UC1, CV_8UC3 or CV_8UC4");
     if (img->width <= 0 || img->height <= 0 || img->pitch < (size_t)img->width * img->channels)
         return fail(HOGB200_BAD_ARG, "bad image size / pitch");
     if (img->width > 32000 || img->height > 32000) return fail(HOGB200_BAD_ARG, "image too large");
@@ -379,6 +381,22 @@ int stage_frame(hogb200* h, const hogb200_image* img, int buf, cudaStream_t st, 
 {
     const int cn = img->channels;
     const size_t row = (size_t)img->width * cn;
+    if (cn == 3) {                   // B,G,R -> B,G,R,255 on the device; host frames travel as 3 bytes per pixel
+        const uint8_t* src = (const uint8_t*)img->data;
+        size_t spitch = img->pitch;
+        if (!img->on_device) {
+            spitch = align_up(row, 64);
+            CK(h->d_raw[buf].reserve(spitch * img->height + 64));
+            CK(cudaMemcpy2DAsync(h->d_raw[buf].p, spitch, img->data, img->pitch, row, img->height, cudaMemcpyHostToDevice, st));
+            src = h->d_raw[buf].p;
+        }
+        const size_t pitch = align_up((size_t)img->width * 4, 64);
+        CK(h->d_frame[buf].reserve(pitch * img->height + 64));
+        launch_bgr_to_bgra(src, spitch, h->d_frame[buf].p, pitch, img->width, img->height, st);
+        CK(cudaGetLastError());
+        out.dev = h->d_frame[buf].p; out.pitch = (int)pitch;
+        return HOGB200_OK;
+    }
     // the kernels read rows in 4-pixel vectors: 16-byte aligned rows for 8UC4, 4-byte for 8UC1, and (so that
     // the last vector of the last row stays inside the caller's buffer) a width that is a multiple of 4
     // unless the pitch leaves room; anything else goes through the staging copy below
@@ -650,6 +668,7 @@ void hogb200_destroy(hogb200_t* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (int i = 0; i < kMaxDet; i++) h->d_det[i].release();
     for (auto& b : h->d_frame) b.release();
+    for (auto& b : h->d_raw) b.release();
     h->d_pyr.release(); h->d_hist.release();
     h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
     for (Plan* P : {&h->plan, &h->plan1, &h->plan_grp}) {
@@ -761,7 +780,7 @@ int run_single(hogb200* h, Plan& P, const hogb200_image* img, bool single, int n
     if ((rc = check_image(img))) return rc;
     if ((rc = check_work_params(h))) return rc;
     if ((rc = use_device(h))) return rc;
-    if ((rc = build_plan(h, P, img->width, img->height, img->channels, single))) return rc;
+    if ((rc = build_plan(h, P, img->width, img->height, img->channels == 3 ? 4 : img->channels, single))) return rc;
     if (ndet > 0 && win_bx(h) != 7 && win_bx(h) != 5)
         return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows 64 (7 blocks) or 48 (5 blocks) pixels wide");
     if (ndet > 0 && win_by(h) > 15) return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows up to 128 pixels high");
@@ -878,7 +897,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         // frames go through the kernels in groups: one launch of each kernel covers `grp` frames, which evens out the
         // tail of the persistent histogram kernel and the last wave of the other two
         const int grp = std::min(batch_group(), nf);
-        if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels, false, grp))) return rc;
+        if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, grp))) return rc;
         Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
         for (int attempt = 0; attempt < 2; attempt++) {
@@ -990,6 +1009,7 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
     H_OR_FAIL;
     int rc;
     if ((rc = check_image(img))) return rc;
+    if (img->channels == 3) return fail(HOGB200_BAD_ARG, "resize: 8UC1 or 8UC4 (the pyramid is built from the widened frame)");
     if (dst_w <= 0 || dst_h <= 0 || !out) return fail(HOGB200_BAD_ARG, "bad destination");
     if ((rc = use_device(h))) return rc;
     cudaStream_t st = h->stream;
@@ -1063,7 +1083,7 @@ int hogb200_window_scores(hogb200_t* h, int slot, const hogb200_image* img, floa
     if ((rc = check_image(img))) return rc;
     if ((rc = check_work_params(h))) return rc;
     if ((rc = use_device(h))) return rc;
-    if ((rc = build_plan(h, h->plan1, img->width, img->height, img->channels, true))) return rc;
+    if ((rc = build_plan(h, h->plan1, img->width, img->height, img->channels == 3 ? 4 : img->channels, true))) return rc;
     const LevelHost& L = h->plan1.lv[0];
     if (wins_x) *wins_x = L.nwx;
     if (wins_y) *wins_y = L.nwy;

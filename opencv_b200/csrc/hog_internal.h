@@ -69,6 +69,9 @@ struct Candidate { int level; int x; int y; float score; };
 int resize_tile_w(int cn);   // tile geometry the host uses to build ResizeItems
 int resize_tile_h(int cn, int rs_rows);
 int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w);
+// 8UC3 (B,G,R) -> 8UC4 (B,G,R,255): the colour conversion example_gpu_tbd does on the host before the upload
+// (samples/gpu/tbd.cpp:573-599), moved to the device.  dst rows are 16-byte aligned.
+void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st);
 void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);

@@ -285,7 +285,40 @@ resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     }
 }
 
+// 8UC3 -> 8UC4, one thread = 4 pixels (three 4-byte loads when the row is 4-byte aligned, one 16-byte store)
+__global__ void __launch_bounds__(256)
+bgr_to_bgra_kernel(const uint8_t* __restrict__ src, size_t spitch, uint8_t* __restrict__ dst, size_t dpitch, int w, int h,
+                   int aligned)
+{
+    const int x4 = 4 * (blockIdx.x * 64 + (threadIdx.x & 63)), y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (x4 >= w || y >= h) return;
+    const uint8_t* __restrict__ s = src + (size_t)y * spitch + 3 * (size_t)x4;
+    uint8_t* __restrict__ d = dst + (size_t)y * dpitch + 4 * (size_t)x4;
+    if (aligned && x4 + 3 < w) {
+        const unsigned a = __ldg(reinterpret_cast<const unsigned*>(s)), b = __ldg(reinterpret_cast<const unsigned*>(s) + 1),
+                       c = __ldg(reinterpret_cast<const unsigned*>(s) + 2);
+        uint4 o;                                   // bytes: B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+        o.x = (a & 0x00ffffffu) | 0xff000000u;
+        o.y = __byte_perm(a, b, 0x0543) | 0xff000000u;
+        o.z = __byte_perm(b, c, 0x0432) | 0xff000000u;
+        o.w = (c >> 8) | 0xff000000u;
+        *reinterpret_cast<uint4*>(d) = o;
+    } else {
+        for (int k = 0; k < 4 && x4 + k < w; k++) {
+            const unsigned v = s[3 * k] | (s[3 * k + 1] << 8) | (s[3 * k + 2] << 16) | 0xff000000u;
+            *reinterpret_cast<unsigned*>(d + 4 * k) = v;
+        }
+    }
+}
+
 }  // namespace
+
+void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st)
+{
+    if (w <= 0 || h <= 0) return;
+    const int aligned = ((uintptr_t)src % 4 == 0) && (spitch % 4 == 0);
+    bgr_to_bgra_kernel<<<dim3((w + 255) / 256, (h + 3) / 4), 256, 0, st>>>(src, spitch, dst, dpitch, w, h, aligned);
+}
 
 int resize_tile_w(int cn) { return cn == 4 ? kRsTileW : 128; }
 int resize_tile_h(int cn, int rs_rows)

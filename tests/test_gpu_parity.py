@@ -213,7 +213,7 @@ def test_empty_detector_and_small_image(port):
     assert len(h.detect(small)) == 0 and len(h.detectMultiScale(small)) == 0
     assert h.compute(small).shape == (0, 3780)
     with pytest.raises(HogError):
-        h.detect(np.zeros((100, 100, 3), np.uint8))                                 # CV_8UC3 is not accepted
+        h.detect(np.zeros((100, 100, 2), np.uint8))                                 # hog.cpp:340 (8UC3 is widened, see below)
     h.setWinStride((12, 8))
     with pytest.raises(HogError):
         h.detect(img)                                                               # hog.cpp:341
@@ -300,6 +300,32 @@ def test_two_detectors_and_batch(hog, port):
     dev = [torch.from_numpy(f).cuda() for f in frames]
     out2 = hog.detectMultiScaleBatch(dev, nslots=2)
     assert all(np.array_equal(a, b) for a, b in zip(out, out2))
+    hog.setHitThreshold(0.0)
+
+
+@pytest.mark.parametrize("shape", [(640, 480), (321, 243), (1242, 375)])
+def test_bgr_input_equals_bgra(hog, port, shape):
+    """8UC3 frames (what example_gpu_tbd reads before its host cvtColor, samples/gpu/tbd.cpp:573-599) are widened on
+    the device: every result equals the one of the 8UC4 frame, host or device input, odd widths and pitches too."""
+    import torch
+    w, h = shape
+    bgra = synthetic_frame(900 + w, w, h, 4, silhouettes=3)
+    bgr = np.ascontiguousarray(bgra[:, :, :3])
+    hog.setHitThreshold(-1.5); hog.setGroupThreshold(0)
+    r4, c4 = hog.detectMultiScale(bgra, confidences=True)
+    r3, c3 = hog.detectMultiScale(bgr, confidences=True)
+    assert len(r4) > 0 and np.array_equal(r3, r4) and np.array_equal(c3, c4)
+    r3d, c3d = hog.detectMultiScale(torch.from_numpy(bgr).cuda(), confidences=True)
+    assert np.array_equal(r3d, r4) and np.array_equal(c3d, c4)
+    wide = np.zeros((h, w + 5, 3), np.uint8); wide[:, :w] = bgr          # a pitched view (pitch = 3 * (w + 5))
+    r3p, c3p = hog.detectMultiScale(torch.from_numpy(wide).cuda()[:, :w], confidences=True)
+    assert np.array_equal(r3p, r4) and np.array_equal(c3p, c4)
+    assert np.array_equal(hog.blockHistograms(bgr), hog.blockHistograms(bgra))
+    hog.setGroupThreshold(2)
+    out = hog.detectMultiScaleBatch([bgr, bgra, bgr])
+    assert np.array_equal(out[0], out[1]) and np.array_equal(out[0], out[2])
+    er, _ = port.detect_multiscale(bgra, hog.getDefaultPeopleDetector(), hit_threshold=-1.5, group_threshold=2)
+    assert abs(len(out[0]) - len(er)) <= 1
     hog.setHitThreshold(0.0)
 
 
