@@ -63,6 +63,26 @@ const char* hogb200_last_error(void);
 const char* hogb200_version(void);
 
 /* ---- lifetime: HOG::create, hog.cpp:682-689 + ctor asserts :252-264.  geom == NULL -> defaults. */
+/* ---- detector files (widening row f3) ------------------------------------------------------------------
+ * The "opencv-object-detector-hog" FileStorage node, XML or YAML by file extension, that
+ * cv::HOGDescriptor::save/load (modules/objdetect/src/hog.cpp:139-209) and cv::cuda::HOG::save/load
+ * (modules/cudaobjdetect/src/hog.cpp:599-679) exchange -- including SVMDetector, which the fork's GPU writer
+ * omits.  Files written here load in the reference and vice versa.  Host-only: no CUDA device is needed. */
+typedef struct hogb200_model {
+    hogb200_geom geom;
+    double win_sigma;          /* < 0: (block_w + block_h) / 8 (getWinSigma, hog.cpp:104-107) */
+    double l2hys_threshold;
+    int gamma_correction;
+    int nlevels;
+} hogb200_model;
+/* objname NULL: the first top-level node (load) / FileStorage::getDefaultObjectName(filename) (save) */
+int hogb200_model_read(const char* filename, const char* objname, hogb200_model* m, float* detector, size_t capacity,
+                       size_t* count);
+int hogb200_model_write(const char* filename, const char* objname, const hogb200_model* m, const float* detector, size_t n);
+/* cv::cuda::HOG::save with the detector of `slot` included; HOG::load as a factory (the geometry is fixed at creation) */
+int hogb200_save(const hogb200_t* h, const char* filename, const char* objname, int slot);
+int hogb200_create_from_file(const char* filename, const char* objname, int device, hogb200_t** out);
+
 int  hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out);
 void hogb200_destroy(hogb200_t* h);
 /* cudaStream_t as void*; NULL restores the handle's private stream.  (HOG::compute's Stream& argument.) */

@@ -96,6 +96,8 @@ struct Plan {
 
 }  // namespace
 
+namespace hogk { int storage_fail(int code, const std::string& msg) { return fail(code, msg); } }
+
 struct hogb200 {
     int device = 0;
     hogb200_geom g;
@@ -105,6 +107,7 @@ struct hogb200 {
     int descr_format = HOGB200_DESCR_FORMAT_COL_BY_COL;
     // detectors: reordered to row-major blocks (hog.cpp:303-317) on the device, bias on the host
     DevBuf<float> d_det[kMaxDet]; float bias[kMaxDet] = {0, 0, 0, 0}; bool have_det[kMaxDet] = {false, false, false, false};
+    std::vector<float> det_host[kMaxDet];           // as given (column-major blocks + optional bias), for hogb200_save
     // streams
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
     cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
@@ -732,7 +735,7 @@ int hogb200_set_svm_detector(hogb200_t* h, int slot, const float* coeffs, size_t
     H_OR_FAIL;
     if (slot < 0 || slot >= kMaxDet) return fail(HOGB200_BAD_ARG, "bad detector slot");
     if (use_device(h)) return HOGB200_CUDA_ERROR;
-    if (n == 0) { CK(cudaStreamSynchronize(h->stream)); h->have_det[slot] = false; return HOGB200_OK; }
+    if (n == 0) { CK(cudaStreamSynchronize(h->stream)); h->have_det[slot] = false; h->det_host[slot].clear(); return HOGB200_OK; }
     const size_t ds = hogb200_get_descriptor_size(h);
     if (!coeffs || (n != ds && n != ds + 1))
         return fail(HOGB200_BAD_ARG, "detector.cols must be descriptor_size or descriptor_size + 1 (hog.cpp:301)");
@@ -747,6 +750,35 @@ int hogb200_set_svm_detector(hogb200_t* h, int slot, const float* coeffs, size_t
     CK(cudaMemcpy(h->d_det[slot].p, re.data(), ds * sizeof(float), cudaMemcpyHostToDevice));
     h->bias[slot] = n > ds ? coeffs[ds] : 0.f;      // hog.cpp:320
     h->have_det[slot] = true;
+    h->det_host[slot].assign(coeffs, coeffs + n);
+    return HOGB200_OK;
+}
+
+int hogb200_save(const hogb200_t* h, const char* filename, const char* objname, int slot)
+{
+    H_OR_FAIL;
+    if (slot < 0 || slot >= kMaxDet) return fail(HOGB200_BAD_ARG, "bad detector slot");
+    hogb200_model m;
+    m.geom = h->g; m.win_sigma = h->win_sigma; m.l2hys_threshold = h->l2hys; m.gamma_correction = h->gamma; m.nlevels = h->nlevels;
+    const std::vector<float>& d = h->det_host[slot];
+    return hogb200_model_write(filename, objname, &m, d.empty() ? nullptr : d.data(), d.size());
+}
+
+int hogb200_create_from_file(const char* filename, const char* objname, int device, hogb200_t** out)
+{
+    if (!out) return fail(HOGB200_BAD_ARG, "out is null");
+    *out = nullptr;
+    hogb200_model m;
+    std::vector<float> det(1 << 16);
+    size_t n = 0;
+    int rc = hogb200_model_read(filename, objname, &m, det.data(), det.size(), &n);
+    if (rc) return rc;
+    hogb200_t* h = nullptr;
+    if ((rc = hogb200_create(&m.geom, device, &h))) return rc;
+    // HOG_Impl::read (cudaobjdetect/src/hog.cpp:599-641): the stored parameters, defaults for the rest
+    h->win_sigma = m.win_sigma; h->l2hys = m.l2hys_threshold; h->gamma = m.gamma_correction; h->nlevels = m.nlevels;
+    if (n && (rc = hogb200_set_svm_detector(h, 0, det.data(), n))) { hogb200_destroy(h); return rc; }
+    *out = h;
     return HOGB200_OK;
 }
 

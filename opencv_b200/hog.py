@@ -35,6 +35,11 @@ class _Image(C.Structure):
                 ("channels", C.c_int), ("on_device", C.c_int)]
 
 
+class _Model(C.Structure):
+    _fields_ = [("geom", _Geom), ("win_sigma", C.c_double), ("l2hys_threshold", C.c_double),
+                ("gamma_correction", C.c_int), ("nlevels", C.c_int)]
+
+
 class Timings(C.Structure):
     _fields_ = [("upload_ms", C.c_float), ("resize_ms", C.c_float), ("hist_ms", C.c_float), ("svm_ms", C.c_float),
                 ("download_ms", C.c_float), ("total_ms", C.c_float), ("kernel_launches", C.c_int),
@@ -93,6 +98,10 @@ def load_library():
     L.hogb200_window_scores.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Image), C.c_void_p, C.c_size_t,
                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.hogb200_group_rectangles.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
+    L.hogb200_model_read.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.hogb200_model_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t]
+    L.hogb200_save.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]
+    L.hogb200_create_from_file.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
     L.hogb200_enable_timing.argtypes = [C.c_void_p, C.c_int]
     L.hogb200_last_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     _LIB = L
@@ -130,6 +139,37 @@ def _as_image(img, keep):
     raise HogError(1, "unsupported image object")
 
 
+def read_model(filename, objname=None):
+    """The "opencv-object-detector-hog" node of an XML / YAML file (cv::HOGDescriptor::load, objdetect/src/hog.cpp:139-203)
+    -> dict of parameters + `detector` (float32 array, empty if the file has none).  Host only."""
+    L = load_library()
+    m = _Model()
+    det = np.zeros(1 << 16, np.float32)
+    n = C.c_size_t(0)
+    rc = L.hogb200_model_read(os.fsencode(filename), objname.encode() if objname else None, C.byref(m),
+                              det.ctypes.data, det.size, C.byref(n))
+    if rc != 0:
+        raise HogError(rc, L.hogb200_last_error().decode())
+    g = m.geom
+    return {"win_size": (g.win_w, g.win_h), "block_size": (g.block_w, g.block_h),
+            "block_stride": (g.block_stride_w, g.block_stride_h), "cell_size": (g.cell_w, g.cell_h), "nbins": g.nbins,
+            "win_sigma": m.win_sigma, "l2hys_threshold": m.l2hys_threshold, "gamma_correction": bool(m.gamma_correction),
+            "nlevels": m.nlevels, "detector": det[:n.value].copy()}
+
+
+def write_model(filename, detector=None, objname=None, win_size=(64, 128), block_size=(16, 16), block_stride=(8, 8),
+                cell_size=(8, 8), nbins=9, win_sigma=-1.0, l2hys_threshold=0.2, gamma_correction=True, nlevels=64):
+    """cv::HOGDescriptor::save (objdetect/src/hog.cpp:176-209), SVMDetector included.  Host only."""
+    L = load_library()
+    m = _Model(_Geom(win_size[0], win_size[1], block_size[0], block_size[1], block_stride[0], block_stride[1],
+                     cell_size[0], cell_size[1], nbins), win_sigma, l2hys_threshold, int(bool(gamma_correction)), nlevels)
+    d = None if detector is None else np.ascontiguousarray(detector, np.float32).ravel()
+    rc = L.hogb200_model_write(os.fsencode(filename), objname.encode() if objname else None, C.byref(m),
+                               d.ctypes.data if d is not None else None, 0 if d is None else d.size)
+    if rc != 0:
+        raise HogError(rc, L.hogb200_last_error().decode())
+
+
 class HOG:
     """cv::cuda::HOG look-alike.  Create with HOG.create(...)."""
     DESCR_FORMAT_COL_BY_COL = 0
@@ -147,6 +187,21 @@ class HOG:
     @classmethod
     def create(cls, win_size=(64, 128), block_size=(16, 16), block_stride=(8, 8), cell_size=(8, 8), nbins=9, device=0):
         return cls(win_size, block_size, block_stride, cell_size, nbins, device)
+
+    @classmethod
+    def load(cls, filename, objname=None, device=0):
+        """cv::cuda::HOG::load (cudaobjdetect/src/hog.cpp:667-672) as a factory; the file's SVMDetector goes to slot 0."""
+        self = cls.__new__(cls)
+        self._L = load_library()
+        self._h = C.c_void_p()
+        self._win = tuple(read_model(filename, objname)["win_size"])
+        self._ck(self._L.hogb200_create_from_file(os.fsencode(filename), objname.encode() if objname else None, device,
+                                                  C.byref(self._h)))
+        return self
+
+    def save(self, filename, objname=None, slot=0):
+        """cv::cuda::HOG::save (hog.cpp:674-678), with the detector of `slot` (which the fork's writer leaves out)."""
+        self._ck(self._L.hogb200_save(self._h, os.fsencode(filename), objname.encode() if objname else None, slot))
 
     def __del__(self):
         try:

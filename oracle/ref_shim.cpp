@@ -14,6 +14,7 @@
 //   cv::HOGDescriptor::detectMultiScale             modules/objdetect/src/hog.cpp:2051-2105
 //   cv::groupRectangles (free function)             modules/objdetect/src/cascadedetect.cpp:366-371
 //   HOGDescriptor::getDefaultPeopleDetector / getDaimlerPeopleDetector   hog.cpp:2174-3487
+//   cv::HOGDescriptor::save / load (FileStorage XML / YAML)              modules/objdetect/src/hog.cpp:139-209
 #include <opencv2/core.hpp>
 #include <opencv2/core/utility.hpp>
 #include <opencv2/imgproc.hpp>
@@ -201,6 +202,35 @@ int cvref_rng_fill(unsigned long long seed, unsigned char* img, int w, int h, in
     Mat m = wrap(img, w, h, cn, pitch);
     rng.fill(m, RNG::UNIFORM, 0, 256);
     return 0;
+    REF_CATCH
+}
+
+// cv::HOGDescriptor::save (objdetect/src/hog.cpp:205-209): "opencv-object-detector-hog" node incl. SVMDetector
+int cvref_hog_save(const char* path, const char* objname, const int* geom, double win_sigma, double l2hys, int gamma,
+                   int nlevels, const float* det, long ndet)
+{
+    REF_TRY
+    HOGDescriptor hog = makeHog(geom, win_sigma, l2hys, gamma, nlevels);
+    if (det && ndet > 0) hog.svmDetector.assign(det, det + ndet);
+    hog.save(path, objname ? objname : "");
+    return 0;
+    REF_CATCH
+}
+
+// cv::HOGDescriptor::load (hog.cpp:198-203).  Returns the detector length (0 = none), -1 on error.
+long cvref_hog_load(const char* path, const char* objname, int* geom, double* win_sigma, double* l2hys, int* gamma,
+                    int* nlevels, float* det, long capacity)
+{
+    REF_TRY
+    HOGDescriptor hog;
+    if (!hog.load(path, objname ? objname : "")) { g_err = "load returned false"; return -1; }
+    geom[0] = hog.winSize.width; geom[1] = hog.winSize.height; geom[2] = hog.blockSize.width; geom[3] = hog.blockSize.height;
+    geom[4] = hog.blockStride.width; geom[5] = hog.blockStride.height; geom[6] = hog.cellSize.width; geom[7] = hog.cellSize.height;
+    geom[8] = hog.nbins;
+    *win_sigma = hog.winSigma; *l2hys = hog.L2HysThreshold; *gamma = hog.gammaCorrection ? 1 : 0; *nlevels = hog.nlevels;
+    if ((long)hog.svmDetector.size() > capacity) { g_err = "capacity"; return -1; }
+    if (!hog.svmDetector.empty()) memcpy(det, hog.svmDetector.data(), hog.svmDetector.size() * sizeof(float));
+    return (long)hog.svmDetector.size();
     REF_CATCH
 }
 

@@ -177,6 +177,27 @@ class Ref:
         n = self._chk(self.L.cvref_people_detector(which, _vp(out), C.c_long(out.size)))
         return out[:n].copy()
 
+    def hog_save(self, path, detector, objname=None, g=DEFAULT_GEOM, nlevels=64):
+        """cv::HOGDescriptor::save of the unmodified reference (objdetect/src/hog.cpp:205-209)."""
+        geom, ws, l2, gamma = self._g(g)
+        d = None if detector is None else np.ascontiguousarray(detector, np.float32)
+        self.L.cvref_hog_save.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.c_double, C.c_double, C.c_int,
+                                          C.c_int, C.c_void_p, C.c_long]
+        self._chk(self.L.cvref_hog_save(os.fsencode(path), objname.encode() if objname else None, geom, ws, l2, gamma,
+                                        nlevels, None if d is None else d.ctypes.data, 0 if d is None else d.size))
+
+    def hog_load(self, path, objname=None):
+        """cv::HOGDescriptor::load of the unmodified reference (hog.cpp:198-203)."""
+        geom = (C.c_int * 9)(); ws = C.c_double(); l2 = C.c_double(); gamma = C.c_int(); nl = C.c_int()
+        det = np.zeros(1 << 16, np.float32)
+        self.L.cvref_hog_load.restype = C.c_long
+        self.L.cvref_hog_load.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_double),
+                                          C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_long]
+        n = self._chk(self.L.cvref_hog_load(os.fsencode(path), objname.encode() if objname else None, geom, C.byref(ws),
+                                            C.byref(l2), C.byref(gamma), C.byref(nl), det.ctypes.data, det.size))
+        return {"geom": list(geom), "win_sigma": ws.value, "l2hys_threshold": l2.value,
+                "gamma_correction": bool(gamma.value), "nlevels": nl.value, "detector": det[:n].copy()}
+
     def rng_fill(self, seed, w, h, cn):
         img = np.zeros((h, w, cn), np.uint8)
         self._chk(self.L.cvref_rng_fill(C.c_ulonglong(seed), _vp(img), w, h, cn, C.c_long(w * cn)))

@@ -329,6 +329,33 @@ def test_bgr_input_equals_bgra(hog, port, shape):
     hog.setHitThreshold(0.0)
 
 
+def test_save_load_detector_file(hog, tmp_path):
+    """cv::cuda::HOG::save / load (cudaobjdetect/src/hog.cpp:599-679) with the detector included: a handle created from
+    the file detects exactly what the original does; the reference's own writer output loads as well."""
+    from opencv_b200 import HOG
+    from _oracle import Ref
+    img = synthetic_frame(31, 640, 480, 4, silhouettes=3)
+    hog.setHitThreshold(-1.0); hog.setGroupThreshold(0); hog.setNumLevels(20)
+    want = hog.detectMultiScale(img, confidences=True)
+    for ext in ("yml", "xml"):
+        path = str(tmp_path / ("people." + ext))
+        hog.save(path)
+        h2 = HOG.load(path)
+        assert h2.getNumLevels() == 20 and h2.getWinSigma() == 4.0 and h2.getGammaCorrection() is True
+        h2.setHitThreshold(-1.0); h2.setGroupThreshold(0)
+        got = h2.detectMultiScale(img, confidences=True)
+        assert len(want[0]) > 0 and np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    if Ref.available():
+        ref = Ref()
+        path = str(tmp_path / "from_reference.yml")
+        ref.hog_save(path, ref.people_detector(0), nlevels=20)
+        h3 = HOG.load(path)
+        h3.setHitThreshold(-1.0); h3.setGroupThreshold(0)
+        got = h3.detectMultiScale(img, confidences=True)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2); hog.setNumLevels(64)
+
+
 def test_dense_candidates_overflow_path(hog, port):
     """hit_threshold far below every score: every window is a candidate (dense-pyramid stress, config 5 in
     small): exercises the candidate-list regrow path and the ordering."""

@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")/.."
 name=$1; shift
 mkdir -p build_variants/$name
-for f in resize hist svm hog_host; do
+for f in resize hist svm hog_host hog_storage; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-O2 "$@" -c opencv_b200/csrc/$f.cu -o build_variants/$name/$f.o &
 done
 wait
