@@ -194,7 +194,12 @@ void resize_table(int src, int dst, bool is_x, std::vector<ResizeCoef>& out)
         const unsigned c0 = (unsigned)(unsigned short)(short)lrintf((1.f - f) * 2048);
         const unsigned c1 = (unsigned)(unsigned short)(short)lrintf(f * 2048);
         ResizeCoef c;
-        if (is_x) { c.s0 = s; c.s1 = std::min(s + 1, src - 1); c.c0 = c0 | (c1 << 16); c.c1 = 0; }
+        if (is_x) {
+            c.s0 = s; c.s1 = std::min(s + 1, src - 1); c.c0 = c0 | (c1 << 16); c.c1 = 0;
+            // the last column has weight (2048, 0): express it as (0, 2048) on columns src-2, src-1, so that the
+            // second tap is ALWAYS the pixel right of the first one and the kernels need a single column pointer
+            if (s >= src - 1 && src >= 2) { c.s0 = src - 2; c.s1 = src - 1; c.c0 = (c0 << 16) | c1; }
+        }
         else      { c.s0 = clip(s, 0, src); c.s1 = clip(s + 1, 0, src); c.c0 = c0 << 16; c.c1 = c1 << 16; }   // rows: :1821-1825
         out.push_back(c);
     }

@@ -10,6 +10,7 @@
 // builds them, so the kernel is integer-only.
 #include "hog_internal.h"
 #include <algorithm>
+#include <cstdlib>
 
 namespace hogk {
 
@@ -46,7 +47,7 @@ constexpr int kRsMaxRows = 16;                              // destination rows 
 constexpr int kRsHeader = 16 + 16 * kRsMaxRows;             // mbarrier + per-row coefficients
 constexpr int kRsWarpBytes = HOGB200_RS_BYTES;                        // staged source pixels per warp
 constexpr int kRsWarpStride = kRsHeader + kRsWarpBytes;
-constexpr int kRsDirectRows = 8;                            // rows per warp of the unstaged paths
+constexpr int kRsDirectRows = 16;                           // rows per warp of the unstaged paths
 
 struct HRow { int t[4]; };        // horizontal result >> 4 of the four channels (resize.cpp:1596: S0[x] >> 4)
 
@@ -110,13 +111,63 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
 }
 
-// One destination row of the unstaged bilinear path (levels too coarse to stage): both taps from global memory.
-__device__ __forceinline__ unsigned direct_px(const uint8_t* __restrict__ base, int bpitch, const ResizeCoef& cx,
-                                              const ResizeCoef& cy)
+struct Px2 { unsigned p0, p1; };
+__device__ __forceinline__ Px2 load_px2(const uint8_t* __restrict__ col, unsigned off)
 {
-    const HRow h0 = hrow_gmem(base + (size_t)cy.s0 * bpitch, cx.s0, cx.s1, cx.c0);
-    const HRow h1 = hrow_gmem(base + (size_t)cy.s1 * bpitch, cx.s0, cx.s1, cx.c0);
-    return vertical_pack(h0, h1, cy.c0, cy.c1);
+    const unsigned* p = reinterpret_cast<const unsigned*>(col + off);
+    Px2 r; r.p0 = __ldg(p); r.p1 = __ldg(p + 1);
+    return r;
+}
+
+// The rows of one warp without staging (see resize_c4_direct_kernel).
+__device__ __forceinline__ void direct_rows(const uint8_t* __restrict__ base, unsigned bpitch, const ResizeCoef& cxa,
+                                            const ResizeCoef& cxb, const ResizeCoef* __restrict__ yt, int nrows,
+                                            uint8_t* __restrict__ dst, int dpitch, bool va, bool vb)
+{
+    const uint8_t* __restrict__ cola = base + 4 * (size_t)cxa.s0;
+    const uint8_t* __restrict__ colb = base + 4 * (size_t)cxb.s0;
+    const unsigned a01a = cxa.c0, a01b = cxb.c0;
+
+    // Two destination rows per iteration, with the roles of the two pixel / horizontal-pass register sets
+    // alternating, so that nothing is copied: row k reads set 0 and fills set 1 with the pixels of row k + 1, row
+    // k + 1 reads set 1 and refills set 0.
+    struct RowRegs { Px2 ua, ub, la, lb; };          // upper source row (when not reused) and lower source row, 2 columns
+    auto request = [&](const ResizeCoef& c, bool reuse_row, RowRegs& r) {
+        r.la = load_px2(cola, (unsigned)c.s1 * bpitch); r.lb = load_px2(colb, (unsigned)c.s1 * bpitch);
+        if (!reuse_row) { r.ua = load_px2(cola, (unsigned)c.s0 * bpitch); r.ub = load_px2(colb, (unsigned)c.s0 * bpitch); }
+    };
+    // computes one destination row from r; Hin = horizontal pass of the previous row's lower source row, Hout = this row's
+    auto emit = [&](const ResizeCoef& c, bool reuse_row, const RowRegs& r, const HRow& Hina, const HRow& Hinb,
+                    HRow& Houta, HRow& Houtb, uint8_t* __restrict__ d) {
+        Houta = hrow_px(r.la.p0, r.la.p1, a01a); Houtb = hrow_px(r.lb.p0, r.lb.p1, a01b);
+        unsigned outa, outb;
+        if (reuse_row) {
+            outa = vertical_pack(Hina, Houta, c.c0, c.c1); outb = vertical_pack(Hinb, Houtb, c.c0, c.c1);
+        } else {
+            const HRow Ua = hrow_px(r.ua.p0, r.ua.p1, a01a), Ub = hrow_px(r.ub.p0, r.ub.p1, a01b);
+            outa = vertical_pack(Ua, Houta, c.c0, c.c1); outb = vertical_pack(Ub, Houtb, c.c0, c.c1);
+        }
+        if (va) *reinterpret_cast<unsigned*>(d) = outa;
+        if (vb) *reinterpret_cast<unsigned*>(d + 128) = outb;
+    };
+    ResizeCoef c0 = yt[0], c1 = yt[min(1, nrows - 1)];
+    RowRegs r0, r1;
+    HRow H0a, H0b, H1a, H1b;
+#pragma unroll
+    for (int c = 0; c < 4; c++) H1a.t[c] = H1b.t[c] = 0;
+    request(c0, false, r0);
+    bool reuse0 = false;                                   // row k reuses the previous row's lower source row
+    for (int k = 0; k < nrows; k += 2, dst += 2 * (size_t)dpitch) {
+        const ResizeCoef c2 = yt[min(k + 2, nrows - 1)], c3 = yt[min(k + 3, nrows - 1)];
+        const bool reuse1 = c1.s0 == c0.s1;                // warp-uniform
+        request(c1, reuse1, r1);                           // row k + 1 (a repeat of the last row when k + 1 == nrows)
+        emit(c0, reuse0, r0, H1a, H1b, H0a, H0b, dst);
+        if (k + 1 >= nrows) break;
+        const bool reuse2 = c2.s0 == c1.s1;
+        request(c2, reuse2, r0);                           // row k + 2
+        emit(c1, reuse1, r1, H0a, H0b, H1a, H1b, dst + dpitch);
+        reuse0 = reuse2; c0 = c2; c1 = c3;
+    }
 }
 
 __global__ void __launch_bounds__(kRsWarps * 32)
@@ -165,12 +216,8 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     const ResizeCoef* __restrict__ xt = xtab + L.xtab_off;
     const ResizeCoef* __restrict__ yt = ytab + L.ytab_off + y0;
     const ResizeCoef cxa = xt[min(xa, w - 1)], cxb = xt[min(xb, w - 1)];
-    if (rs == 0) {              // unstaged: a level so coarse that one row pair of the tile exceeds the slice
-        for (int k = 0; k < nrows; k++, dst += dpitch) {
-            const ResizeCoef cy = yt[k];
-            if (va) *reinterpret_cast<unsigned*>(dst) = direct_px(base, bpitch, cxa, cy);
-            if (vb) *reinterpret_cast<unsigned*>(dst + 128) = direct_px(base, bpitch, cxb, cy);
-        }
+    if (rs == 0) {              // unstaged: levels where staging does not pay (few rows per warp would fit the slice)
+        direct_rows(base, (unsigned)bpitch, cxa, cxb, yt, nrows, dst, dpitch, va, vb);
         return;
     }
 
@@ -235,6 +282,60 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
         if (va) *reinterpret_cast<unsigned*>(dst) = outa;
         if (vb) *reinterpret_cast<unsigned*>(dst + 128) = outb;
     }
+}
+
+// 8UC4 without staging: a warp owns 64 columns x 16 rows (lane <-> columns x, x+32) and walks down; both taps of a
+// pixel come from one per-thread column pointer (the host table guarantees s1 == s0 + 1), the source rows of the
+// NEXT destination row are requested before the current one is computed (so L2 latency hides behind arithmetic),
+// and the horizontal pass of the lower source row is kept for the next destination row, which reuses it whenever
+// its upper row is that row (always below scale ~1.5).
+constexpr int kRdWarps = 4, kRdRows = 16;
+
+__global__ void __launch_bounds__(kRdWarps * 32)
+resize_c4_direct_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels,
+                        const ResizeCoef* __restrict__ xtab, const ResizeCoef* __restrict__ ytab,
+                        const ResizeItem* __restrict__ items)
+{
+    const ResizeItem it = items[blockIdx.x];
+    if (it.frame >= fs.nframes) return;
+    const uint8_t* __restrict__ base = fs.base[it.frame];
+    const unsigned bpitch = (unsigned)fs.pitch[it.frame];
+    const LevelDesc& L = levels[it.level];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int w = L.w, h = L.h;
+    const int y0 = it.y0 + warp * kRdRows;
+    if (y0 >= h) return;                                     // the whole warp
+    const int nrows = min(kRdRows, h - y0);
+    const int xa = it.x0 + lane, xb = xa + 32;
+    const bool va = xa < w, vb = xb < w;
+    const int dpitch = L.pitch;
+    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y0 * dpitch + 4 * xa;
+
+    if (L.mode == 2) {          // exact half: 2x2 box average (resize.cpp:2542-2578)
+        for (int k = 0; k < nrows; k++, dst += dpitch) {
+            const int y = y0 + k;
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                const int x = xa + 32 * c;
+                if (x >= w) continue;
+                const uint2 a = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y) * bpitch) + x);
+                const uint2 b = __ldg(reinterpret_cast<const uint2*>(base + (size_t)(2 * y + 1) * bpitch) + x);
+                unsigned o = 0;
+#pragma unroll
+                for (int ch = 0; ch < 4; ch++) {
+                    const unsigned sum = ((a.x >> (8 * ch)) & 255u) + ((a.y >> (8 * ch)) & 255u) +
+                                         ((b.x >> (8 * ch)) & 255u) + ((b.y >> (8 * ch)) & 255u) + 2u;
+                    o |= (sum >> 2) << (8 * ch);
+                }
+                *reinterpret_cast<unsigned*>(dst + 128 * c) = o;
+            }
+        }
+        return;
+    }
+    const ResizeCoef* __restrict__ xt = xtab + L.xtab_off;
+    const ResizeCoef* __restrict__ yt = ytab + L.ytab_off + y0;
+    const ResizeCoef cxa = xt[min(xa, w - 1)], cxb = xt[min(xb, w - 1)];
+    direct_rows(base, bpitch, cxa, cxb, yt, nrows, dst, dpitch, va, vb);
 }
 
 // 8UC1: one thread = four consecutive destination pixels (one 4-byte store); tile 128 x 8.
@@ -320,10 +421,17 @@ void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t 
     bgr_to_bgra_kernel<<<dim3((w + 255) / 256, (h + 3) / 4), 256, 0, st>>>(src, spitch, dst, dpitch, w, h, aligned);
 }
 
+// HOGB200_RS_DIRECT=1: every 8UC4 level through the unstaged kernel (64 x 64 tiles)
+bool resize_direct()
+{
+    static const bool on = [] { const char* e = getenv("HOGB200_RS_DIRECT"); return e && atoi(e) != 0; }();
+    return on;
+}
 int resize_tile_w(int cn) { return cn == 4 ? kRsTileW : 128; }
 int resize_tile_h(int cn, int rs_rows)
 {
     if (cn != 4) return 8;
+    if (resize_direct()) return kRdWarps * kRdRows;
     return kRsWarps * (rs_rows > 0 ? rs_rows : (rs_rows < 0 ? -rs_rows : kRsDirectRows));
 }
 
@@ -340,7 +448,9 @@ int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int 
         span = std::max(span, sp);
     }
     const int rowbytes = 4 * span, slack = 16;      // the second tap of the last column may lie one pixel past the span
-    for (int R = kRsMaxRows; R >= 1; R >>= 1) {
+    // staging pays only when the per-warp setup (mbarrier, one bulk copy per source row) is spread over enough rows
+    static const int min_rows = [] { const char* e = getenv("HOGB200_RS_MINROWS"); return e ? atoi(e) : 8; }();
+    for (int R = kRsMaxRows; R >= std::max(1, min_rows); R >>= 1) {
         int range = 0;
         for (int y0 = 0; y0 < dst_h; y0 += R)
             range = std::max(range, yt[std::min(y0 + R, dst_h) - 1].s1 - yt[y0].s0 + 1);
@@ -356,7 +466,9 @@ void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const ResizeItem* d_items, int nitems, cudaStream_t st)
 {
     if (nitems <= 0) return;
-    if (cn == 4) {
+    if (cn == 4 && resize_direct()) {
+        resize_c4_direct_kernel<<<nitems, kRdWarps * 32, 0, st>>>(fs, d_levels, d_xtab, d_ytab, d_items);
+    } else if (cn == 4) {
         constexpr int smem = kRsWarps * kRsWarpStride + 16;
         if (smem > 48 * 1024) cudaFuncSetAttribute(resize_c4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         resize_c4_kernel<<<nitems, kRsWarps * 32, smem, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
