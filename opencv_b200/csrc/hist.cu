@@ -22,7 +22,7 @@
 //     read-modify-writes each (bin0 += mag*(1-a), bin0+1 += mag*a); a tenth accumulator row takes the second vote
 //     of bin 8 and is folded into bin 0 by the horizontal pass;
 //   * orientation binning is branch- and conversion-free: angle in bin units with its sign taken from
-//     sign(dx)^sign(dy), floor() by the 1.5*2^23 magic add, whose mantissa is at the same time the shared-memory
+//     sign(dx)^sign(dy), floor() by the 2^23+16 magic add, whose mantissa is at the same time the shared-memory
 //     row offset of the bin (no wrap needed: the 9 reachable rows are a cyclic rotation of the 9 bins);
 //   * every 4 rows one accumulator slot is complete; a HORIZONTAL pass (lane <-> (row, cell)) contracts the 120
 //     columns with the 24-tap horizontal weights into the four cell sums of 14 blocks;
@@ -46,21 +46,22 @@ constexpr int kWarps = HOGB200_HIST_WARPS;         // independent workers per CT
 constexpr int kThreads = kWarps * 32;
 constexpr int kTileCells = 15;                     // 30 voting lanes x 4 columns = 120 columns
 constexpr int kTileBlocks = kTileCells - 1;        // 14 blocks per tile row
-constexpr int kStripBlocks = 8;                    // block rows per work item
 constexpr int kLutCopies = HOGB200_LUT_COPIES;     // gamma LUT replication (bank spreading)
 constexpr int kPF = 4;                             // rows of load prefetch
 
 constexpr int kRows = kBins + 1;                   // accumulator rows per slot: row 9 aliases row 0 (second vote of row 8)
 constexpr int kBinBytes = 4 * 32 * 4;              // one accumulator row: [j][idx] float = 512 B
 constexpr int kSlotBytes = kRows * kBinBytes;      // 5120 B
-constexpr float kMagic = 12582912.f;               // 1.5 * 2^23
+constexpr float kMagic = 8388624.f;                // 2^23 + 16: q + kMagic has ulp 1 for q in [-4.5, 4.5], mantissa = 16 + n
 
 struct __align__(16) WarpSmem {
     float acc[3][kRows][4][32];                    // 15,360 B  vertical partial sums
     float stg[kTileBlocks * kHist];                //  2,016 B  horizontal results of one block row
 };
 struct __align__(16) Smem {
-    float4 wrow[8];                                //    128 B  vertical weights of row o of a cell row: (R, Q, P/T, -)
+    float4 wrow[3][8];                             //    384 B  vertical weights of row o of a cell row, per slot, for the
+                                                   //           three role rotations (slot roles rotate, slots stay put)
+    float4 wh[6];                                  //     96 B  horizontal weights, paired like the accumulator loads
     float lut[256 * kLutCopies];                   // 16,384 B  gamma LUT, lut[v*copies + lane%copies]
     WarpSmem w[kWarps];                            // 12 x 17,376 B
 };
@@ -78,17 +79,20 @@ __device__ __forceinline__ void sts64(unsigned a, float2 v)
     asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a), "f"(v.x), "f"(v.y));
 }
 // one vote = two adjacent accumulator rows (bin0 and bin0 + 1), 512 B apart
+// OFF = byte offset of the slot: the three slots sit at fixed immediates from one address register
+template <int OFF>
 __device__ __forceinline__ float2 lds32x2(unsigned a)
 {
     float2 v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v.x) : "r"(a));
-    asm volatile("ld.shared.f32 %0, [%1+512];" : "=f"(v.y) : "r"(a));
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v.x) : "r"(a), "n"(OFF));
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v.y) : "r"(a), "n"(OFF + 512));
     return v;
 }
+template <int OFF>
 __device__ __forceinline__ void sts32x2(unsigned a, float2 v)
 {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v.x));
-    asm volatile("st.shared.f32 [%0+512], %1;" ::"r"(a), "f"(v.y));
+    asm volatile("st.shared.f32 [%0+%1], %2;" ::"r"(a), "n"(OFF), "f"(v.x));
+    asm volatile("st.shared.f32 [%0+%1], %2;" ::"r"(a), "n"(OFF + 512), "f"(v.y));
 }
 __device__ __forceinline__ void sts64_zero(unsigned a)
 {
@@ -110,6 +114,18 @@ __device__ __forceinline__ float2 fma2(float w, float2 b, float2 c)
 {
     unsigned long long rw, rb, rc, rd;
     asm("mov.b64 %0, {%1,%1};" : "=l"(rw) : "f"(w));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(rw), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+
+__device__ __forceinline__ float2 fma2v(float2 w, float2 b, float2 c)
+{
+    unsigned long long rw, rb, rc, rd;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(rw) : "f"(w.x), "f"(w.y));
     asm("mov.b64 %0, {%1,%2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
     asm("mov.b64 %0, {%1,%2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(rw), "l"(rb), "l"(rc));
@@ -178,7 +194,7 @@ __device__ __forceinline__ void unpack<1>(const unsigned int& raw, const unsigne
     for (int j = 0; j < 4; j++) v[j][0] = lutl[__byte_perm(raw, 0, 0x4440 + j) * kLutCopies];
 }
 
-struct Vote { unsigned off; float g0, g1; };
+struct Vote { unsigned rbits; float g0, g1; };
 
 // One pixel: centred differences, strongest channel, magnitude, orientation in bin units, interpolation weights.
 // NC = channels examined.  xm = 0 on the first / last column (reflect-101 makes dx zero there, hog.cpp:306-313).
@@ -231,7 +247,7 @@ __device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], 
     const float nf = r - kMagic;
     const float alpha = (q - nf) + 0.5f;
     Vote v;
-    v.off = __float_as_uint(r) << 9;
+    v.rbits = __float_as_uint(r);
     v.g1 = mag * alpha;
     v.g0 = mag - v.g1;
     return v;
@@ -239,31 +255,33 @@ __device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], 
 
 // Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row) into the staging plane;
 // also zeroes the accumulator for its next use.  lane <-> (accumulator row, cell): 2 rows x 15 cells per pass.
-__device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws, int cy, const BlockWeights& W, int lane)
+__device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws, int cy, const float4* __restrict__ wh, int lane)
 {
     const int cell = lane & 15, half = lane >> 4;
-    float a0[8], a18[8], a08[4], a1[4];
+    // weights paired like the loads below: (column j, column 4 + j) of the cell
+    // (registers, loaded from shared memory: FFMA2 takes no constant-bank operand)
+    float2 w00[4], w11[4], wx[4];
 #pragma unroll
-    for (int p = 0; p < 8; p++) { a0[p] = W.a0[p]; a18[p] = W.a1[8 + p]; }
-#pragma unroll
-    for (int p = 0; p < 4; p++) { a08[p] = W.a0[8 + p]; a1[p] = W.a1[4 + p]; }
+    for (int j = 0; j < 2; j++) {
+        const float4 a = wh[j], b = wh[2 + j], c = wh[4 + j];
+        w00[2 * j] = make_float2(a.x, a.y); w00[2 * j + 1] = make_float2(a.z, a.w);
+        w11[2 * j] = make_float2(b.x, b.y); w11[2 * j + 1] = make_float2(b.z, b.w);
+        wx[2 * j] = make_float2(c.x, c.y);  wx[2 * j + 1] = make_float2(c.z, c.w);
+    }
 #pragma unroll
     for (int it = 0; it < 5; it++) {
         const int row = it * 2 + half;
         const bool act = row < kBins;        // row 9 only exists as the alias of row 0, folded in below
         // lanes of cell 15 read (and clear) the two halo elements: whatever they hold only reaches sums nobody stores
         const unsigned base = slot_addr + row * kBinBytes + cell * 8;
-        float v[8];
+        float2 v[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const float2 t = lds64(base + j * 128);               // columns j and 4+j of the cell
-            v[j] = t.x; v[4 + j] = t.y;
-        }
+        for (int j = 0; j < 4; j++) v[j] = lds64(base + j * 128);  // columns j and 4+j of the cell
         if (it == 0 && half == 0) {          // row 0 += row 9 (second votes of row 8: both are the same bin)
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const float2 t = lds64(base + 9 * kBinBytes + j * 128);
-                v[j] += t.x; v[4 + j] += t.y;
+                v[j].x += t.x; v[j].y += t.y;
                 sts64_zero(base + 9 * kBinBytes + j * 128);
             }
         }
@@ -271,14 +289,14 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
 #pragma unroll
             for (int j = 0; j < 4; j++) sts64_zero(base + j * 128);
         }
-        float s00 = 0.f, s11 = 0.f, s01 = 0.f, s10 = 0.f;
+        float2 p00 = make_float2(0.f, 0.f), p11 = p00, px = p00;
 #pragma unroll
-        for (int p = 0; p < 8; p++) {
-            s00 = fmaf(a0[p], v[p], s00);                          // cell k = cx0 of block k
-            s11 = fmaf(a18[p], v[p], s11);                         // cell k = cx1 of block k-1
-            if (p < 4) s01 = fmaf(a08[p], v[p], s01);              // -> cx0 of block k-1
-            else       s10 = fmaf(a1[p - 4], v[p], s10);           // -> cx1 of block k
+        for (int j = 0; j < 4; j++) {
+            p00 = fma2v(w00[j], v[j], p00);
+            p11 = fma2v(w11[j], v[j], p11);
+            px = fma2v(wx[j], v[j], px);
         }
+        const float s00 = p00.x + p00.y, s11 = p11.x + p11.y, s01 = px.x, s10 = px.y;
         // block k, cx=0 = own s00 + s01 of cell k+1 ; block k-1, cx=1 = own s11 + s10 of cell k-1
         const float ax = s00 + __shfl_down_sync(0xffffffffu, s01, 1);
         const float bx = s11 + __shfl_up_sync(0xffffffffu, s10, 1);
@@ -363,10 +381,16 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
     // accumulator slots: roles P (block row above, cell row 0), Q (above, cell row 1), R (this, cell row 0);
     // lane l votes into element (l-1)&31 of every [bin][j] row, rows of one slot are 1024 B apart
     const unsigned acc0 = (unsigned)__cvta_generic_to_shared(&ws.acc[0][0][0][0]);
-    // + 4 rows: row index = n + 4; 0x80000000 cancels bit 22 of the magic constant, which `<< 9` leaves in bit 31
-    const unsigned lane_off = ((lane - 1) & 31) * 4 + 4 * kBinBytes + 0x80000000u;
-    unsigned sp = acc0, sq = acc0 + kSlotBytes, sr = acc0 + 2 * kSlotBytes;
-    zero_slot(sr, lane);                                    // P and Q are cleared during the first cell row
+    // row index = n + 4, the mantissa of r holds n + 16 (the exponent bits leave through the `<< 9`)
+    const unsigned lane_off = ((lane - 1) & 31) * 4 + (4 - 16) * kBinBytes;
+    // The slots stay at fixed offsets 0, 1, 2 x kSlotBytes from one address register (immediates in the inner loop);
+    // what rotates after every cell row is which role a slot plays, i.e. which weight column it is fed with:
+    // rot = 0: (P,Q,R) = slots (0,1,2); 1: (2,0,1); 2: (1,2,0).
+    unsigned colbase[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) colbase[j] = acc0 + lane_off + j * 128;
+    int rot = 0, slot_p = 0;
+    zero_slot(acc0 + 2 * kSlotBytes, lane);                 // R; P and Q are cleared during the first cell row
     __syncwarp();
 
     int y = it.by0 * kCell;
@@ -387,11 +411,11 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
     for (int cr = 0; cr <= it.nby; cr++) {
 #pragma unroll 1
         for (int hf = 0; hf < 2; hf++) {
-            float wr[4], wq[4], wp[4];
+            float w0[4], w1[4], w2[4];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const float4 t = s.wrow[hf * 4 + k];
-                wr[k] = t.x; wq[k] = t.y; wp[k] = t.z;
+                const float4 t = s.wrow[rot][hf * 4 + k];
+                w0[k] = t.x; w1[k] = t.y; w2[k] = t.z;
             }
 #pragma unroll
             for (int k = 0; k < 4; k++, y++) {
@@ -418,29 +442,33 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
                 v[2] = pixel<NC>(C[1], C[3], U[2], D[2], xm[2]);
                 v[3] = pixel<NC>(C[2], rt, U[3], D[3], xm[3]);
                 // ---- vertical accumulation: 12 private read-modify-writes, loads first
-                float2 ar[4], aq[4], ap[4];
+                float2 a0[4], a1[4], a2[4];
                 unsigned ad[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    ad[j] = v[j].off + lane_off + j * 128;
-                    ar[j] = lds32x2(ad[j] + sr); aq[j] = lds32x2(ad[j] + sq); ap[j] = lds32x2(ad[j] + sp);
+                    ad[j] = (v[j].rbits << 9) + colbase[j];
+                    a0[j] = lds32x2<0>(ad[j]); a1[j] = lds32x2<kSlotBytes>(ad[j]); a2[j] = lds32x2<2 * kSlotBytes>(ad[j]);
                 }
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const float2 g = make_float2(v[j].g0, v[j].g1);
-                    ar[j] = fma2(wr[k], g, ar[j]); aq[j] = fma2(wq[k], g, aq[j]); ap[j] = fma2(wp[k], g, ap[j]);
+                    a0[j] = fma2(w0[k], g, a0[j]); a1[j] = fma2(w1[k], g, a1[j]); a2[j] = fma2(w2[k], g, a2[j]);
                 }
 #pragma unroll
-                for (int j = 0; j < 4; j++) { sts32x2(ad[j] + sr, ar[j]); sts32x2(ad[j] + sq, aq[j]); sts32x2(ad[j] + sp, ap[j]); }
+                for (int j = 0; j < 4; j++) {
+                    sts32x2<0>(ad[j], a0[j]); sts32x2<kSlotBytes>(ad[j], a1[j]); sts32x2<2 * kSlotBytes>(ad[j], a2[j]);
+                }
 #pragma unroll
                 for (int j = 0; j < 4; j++)
 #pragma unroll
                     for (int c = 0; c < NC; c++) { U[j][c] = C[j][c]; C[j][c] = D[j][c]; }
             }
             __syncwarp();
-            const unsigned done = hf ? sq : sp;             // P is complete after 4 rows, Q after 8
+            // P is complete after 4 rows, Q (the slot after P) after 8
+            const int ds = slot_p + hf >= 3 ? slot_p + hf - 3 : slot_p + hf;
+            const unsigned done = acc0 + ds * kSlotBytes;
             if (cr == 0) zero_slot(done, lane);
-            else horizontal_pass(done, ws, hf, W, lane);
+            else horizontal_pass(done, ws, hf, s.wh, lane);
             __syncwarp();
             if (hf && cr > 0) {
                 const int by = it.by0 + cr - 1;
@@ -449,7 +477,8 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
             }
         }
         // rotate roles: R -> P, T (in P's slot) -> Q, Q's slot (just consumed and zeroed) -> R
-        const unsigned t = sp; sp = sr; sr = sq; sq = t;
+        rot = rot == 2 ? 0 : rot + 1;
+        slot_p = slot_p == 0 ? 2 : slot_p - 1;
     }
 }
 
@@ -468,11 +497,25 @@ hist_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ l
         const float v = (float)(i / kLutCopies);
         s.lut[i] = gamma ? sqrtf(v) : v;
     }
-    if (tid < 8) {
+    if (tid >= 32 && tid < 44) {
+        // pair j = (column j, column 4 + j) of a cell: [0..3] cell k = cx0 of block k; [4..7] cell k = cx1 of block
+        // k-1; [8..11] columns 0..3 -> cx0 of block k-1, columns 4..7 -> cx1 of block k
+        const int j = (tid - 32) & 3, g = (tid - 32) >> 2;
+        float2* wh = reinterpret_cast<float2*>(s.wh);
+        wh[g * 4 + j] = g == 0 ? make_float2(W.a0[j], W.a0[4 + j])
+                      : g == 1 ? make_float2(W.a1[8 + j], W.a1[12 + j])
+                               : make_float2(W.a0[8 + j], W.a1[4 + j]);
+    }
+    if (tid < 24) {
         // row o of a cell row feeds R: block row cr, cell row 0, i = o;  Q: block row cr-1, cell row 1, i = 8+o;
         // P (o<4): block row cr-1, cell row 0, i = 8+o  or  T (o>=4): block row cr, cell row 1, i = o
-        const int o = tid;
-        s.wrow[o] = make_float4(W.a0[o], W.a1[8 + o], o < 4 ? W.a0[8 + o] : W.a1[o], 0.f);
+        const int o = tid & 7, r = tid >> 3;
+        const float wR = W.a0[o], wQ = W.a1[8 + o], wP = o < 4 ? W.a0[8 + o] : W.a1[o];
+        // rotation r: P sits in slot (3 - r) % 3, Q in the next, R in the one after
+        const float x = r == 0 ? wP : r == 1 ? wQ : wR;     // slot 0
+        const float y = r == 0 ? wQ : r == 1 ? wR : wP;     // slot 1
+        const float z = r == 0 ? wR : r == 1 ? wP : wQ;     // slot 2
+        s.wrow[r][o] = make_float4(x, y, z, 0.f);
     }
     __syncthreads();
 
