@@ -227,9 +227,9 @@ def test_empty_detector_and_small_image(port):
 
 
 # ------------------------------------------------------------------ detectMultiScale
-def _set_equal_mod_threshold(hog, port, img, det, hit, group, scale0=1.05, nlevels=64):
+def _set_equal_mod_threshold(hog, port, img, det, hit, group, scale0=1.05, nlevels=64, slot=0):
     hog.setHitThreshold(hit); hog.setGroupThreshold(group); hog.setScaleFactor(scale0); hog.setNumLevels(nlevels)
-    got = hog.detectMultiScale(img)
+    got = hog.detectMultiScale(img, slot=slot)
     exp, _ = port.detect_multiscale(img, det, hit_threshold=hit, scale0=scale0, nlevels=nlevels, group_threshold=group)
     if np.array_equal(got, exp):
         return True, got, exp
@@ -238,7 +238,7 @@ def _set_equal_mod_threshold(hog, port, img, det, hit, group, scale0=1.05, nleve
     lo, _ = port.detect_multiscale(img, det, hit_threshold=hit - SCORE_TOL, scale0=scale0, nlevels=nlevels, group_threshold=0)
     hi, _ = port.detect_multiscale(img, det, hit_threshold=hit + SCORE_TOL, scale0=scale0, nlevels=nlevels, group_threshold=0)
     hog.setGroupThreshold(0)
-    raw = hog.detectMultiScale(img)
+    raw = hog.detectMultiScale(img, slot=slot)
     hog.setGroupThreshold(group)
     s_lo = set(map(tuple, lo)); s_hi = set(map(tuple, hi)); s_raw = set(map(tuple, raw))
     ok = s_hi <= s_raw <= s_lo and len(s_lo - s_hi) > 0
@@ -396,3 +396,68 @@ def test_full_size_1080p_properties(hog, port):
     got = c[off:off + exp.size].reshape(exp.shape)
     assert np.abs(got - exp).max() <= SCORE_TOL
     hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def _dense_full_size(hog, port, img, scale, nlevels, expect_windows, spot_levels):
+    """Every window of every level (hit threshold below all scores, no grouping): the count, the level-0 scores
+    against windowScores, and whole levels end to end (resize -> histograms -> scores) against the oracle."""
+    H, W = img.shape[:2]
+    det = hog.getDefaultPeopleDetector()
+    hog.setScaleFactor(scale); hog.setNumLevels(nlevels); hog.setHitThreshold(-100.0); hog.setGroupThreshold(0)
+    try:
+        r, c = hog.detectMultiScale(img, confidences=True)
+        sc, lw, lh = hog.levels(W, H)
+        per_level = [parts(int(w), 64, 8) * parts(int(h), 128, 8) for w, h in zip(lw, lh)]
+        assert len(r) == sum(per_level) == expect_windows
+        ws = hog.windowScores(img)
+        assert np.array_equal(c[:per_level[0]].astype(np.float32).reshape(ws.shape), ws)
+        # rects of a level: cvRound(x*s), cvRound(y*s), cvRound(64*s), cvRound(128*s) in row-major window order
+        for lvl in spot_levels:
+            off = sum(per_level[:lvl])
+            limg = port.resize(img, int(lw[lvl]), int(lh[lvl]))
+            exp = port.scores(limg, det)
+            got = c[off:off + exp.size].reshape(exp.shape)
+            assert np.abs(got - exp).max() <= SCORE_TOL
+            s = float(sc[lvl])
+            assert tuple(r[off]) == (0, 0, int(np.rint(64 * s)), int(np.rint(128 * s)))
+            assert tuple(r[off + 1][:2]) == (int(np.rint(8 * s)), 0)
+    finally:
+        hog.setScaleFactor(1.05); hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_full_size_4k_properties(hog, port):
+    """BASELINE config 4 (3840x2160 8UC4): 58 levels, 1 209 184 windows."""
+    img = synthetic_frame(4000, 3840, 2160, 4, silhouettes=8)
+    _dense_full_size(hog, port, img, 1.05, 64, 1209184, [31, 57])
+
+
+def test_full_size_dense_pyramid_properties(hog, port):
+    """BASELINE config 5 (1080p, scale 1.02, nlevels 128, hit 0 -> all-pass, group 0): 108 levels, 623 442
+    candidate windows through the compaction / regrow / ordering path."""
+    img = synthetic_frame(5000, 1920, 1080, 4, silhouettes=8)
+    _dense_full_size(hog, port, img, 1.02, 128, 623442, [53, 107])
+
+
+def test_full_size_kitti_sequence_two_detectors(hog, port):
+    """BASELINE config 3 in the sample's shape: a 1242x375 sequence, pedestrian + (synthetic) vehicle detector, the
+    sample's nlevels=15 and nlevels=64: the batch path over a ragged group count equals the per-frame path, and the
+    per-frame path equals the oracle on the first frame."""
+    rng = np.random.RandomState(11)
+    veh = (rng.randn(3781) * 0.05).astype(np.float32); veh[3780] = -0.5
+    det = hog.getDefaultPeopleDetector()
+    hog.setSVMDetector(veh, slot=1)
+    frames = [synthetic_frame(7000 + i, 1242, 375, 4, silhouettes=4) for i in range(11)]    # 2 groups of 4 + 3
+    try:
+        for nlevels, nlv in ((15, 15), (64, 23)):
+            hog.setNumLevels(nlevels); hog.setHitThreshold(-0.75); hog.setGroupThreshold(2)
+            assert len(hog.levels(1242, 375)[0]) == nlv
+            out = hog.detectMultiScaleBatch(frames, nslots=2)
+            assert len(out) == 22
+            for i, f in enumerate(frames):
+                assert np.array_equal(out[2 * i], hog.detectMultiScale(f, slot=0))
+                assert np.array_equal(out[2 * i + 1], hog.detectMultiScale(f, slot=1))
+            for slot, d in ((0, det), (1, veh)):
+                ok, got, exp = _set_equal_mod_threshold(hog, port, frames[0], d, -0.75, 2, 1.05, nlevels, slot=slot)
+                assert ok
+    finally:
+        hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
