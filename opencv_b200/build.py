@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhogb200.so")
-SOURCES = ["resize.cu", "hist.cu", "svm.cu", "hog_host.cu", "hog_storage.cu"]
+SOURCES = ["resize.cu", "hist.cu", "svm.cu", "hog_host.cu", "hog_storage.cu", "tbd_host.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-O2", "--use_fast_math=false"]
@@ -16,7 +16,7 @@ def needs_build():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "hogb200.h"), __file__]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", h) for h in ("hogb200.h", "tbdb200.h")] + [__file__]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -27,7 +27,7 @@ def build(force=False, verbose=False):
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for s in SOURCES:
-        o = os.path.join(HERE, "build", s.replace(".cu", ".o"))
+        o = os.path.join(HERE, "build", os.path.splitext(s)[0] + ".o")
         cmd = [NVCC] + [f for f in FLAGS if not f.startswith("--use_fast_math")] + (["-Xptxas", "-v"] if verbose else []) + \
               ["-c", os.path.join(CSRC, s), "-o", o]
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

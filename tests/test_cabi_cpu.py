@@ -14,13 +14,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_library_exports_every_declared_symbol():
-    hdr = open(os.path.join(ROOT, "include", "hogb200.h")).read()
-    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    names = set(re.findall(r"\b(hogb200_[a-z0-9_]+)\s*\(", hdr))
-    assert len(names) >= 38
     L = C.CDLL(lib_path())
-    missing = [n for n in sorted(names) if not hasattr(L, n)]
-    assert not missing, missing
+    for header, prefix, at_least in (("hogb200.h", "hogb200_", 38), ("tbdb200.h", "tbdb200_", 14)):
+        hdr = open(os.path.join(ROOT, "include", header)).read()
+        hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+        names = set(re.findall(r"\b(%s[a-z0-9_]+)\s*\(" % prefix, hdr))
+        assert len(names) >= at_least, (header, len(names))
+        missing = [n for n in sorted(names) if not hasattr(L, n)]
+        assert not missing, missing
 
 
 def test_create_fails_loudly_without_gpu():

@@ -1,0 +1,211 @@
+"""Tracking-by-detection step: opencv_b200's tbdb200_* (host C++ behind include/tbdb200.h)
+against the UNMODIFIED reference cv::tbd::Tracker compiled into oracle/_ref/libcvref.so (oracle/ref_tbd_shim.cpp),
+on the same seeded detection sequences, and against the golden fixture recorded from the reference
+(tests/golden/tbd_golden.npz, made by tests/golden/make_tbd_golden.py).  Everything is compared after every step and
+must be IDENTICAL: integer boxes, double confidences / overlaps (same operations in the same order), metrics.
+Host code: these run without a GPU."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from _oracle import REF_SO
+from opencv_b200 import tbd
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tbd_golden.npz")
+
+
+class RefTracker:
+    def __init__(self, a):
+        self.L = C.CDLL(REF_SO)
+        self.L.cvref_tbd_create.restype = C.c_void_p
+        self.L.cvref_tbd_create.argtypes = [C.c_double, C.c_uint, C.c_uint, C.c_double, C.c_double, C.c_int]
+        for f in ("destroy", "reset", "step", "num_tracks", "get_tracks", "track_history", "snapshot", "restore", "metrics"):
+            getattr(self.L, "cvref_tbd_" + f).argtypes = None
+        self.h = C.c_void_p(self.L.cvref_tbd_create(a.costOfNonAssignment, a.timeWindowSize, a.trackAgeThreshold,
+                                                    a.trackVisibilityThreshold, a.trackConfidenceThreshold,
+                                                    a.shouldStoreMetrics))
+
+    def __del__(self):
+        self.L.cvref_tbd_destroy(self.h)
+
+    def step(self, dets, frame_id):
+        n = len(dets)
+        ints = np.array([[d.id, d.frame_id, d.x, d.y, d.width, d.height] for d in dets], np.int32).reshape(-1)
+        conf = np.array([d.confidence for d in dets], np.float64)
+        self.L.cvref_tbd_step(self.h, ints.ctypes.data_as(C.c_void_p), conf.ctypes.data_as(C.c_void_p), C.c_int(n), C.c_int(frame_id))
+
+    def state(self):
+        """[(13 ints, 3 doubles, frames, boxes, scores)] per track"""
+        n = self.L.cvref_tbd_num_tracks(self.h)
+        ints = np.zeros((max(n, 1), 13), np.int32); dbl = np.zeros((max(n, 1), 3), np.float64)
+        self.L.cvref_tbd_get_tracks(self.h, ints.ctypes.data_as(C.c_void_p), dbl.ctypes.data_as(C.c_void_p))
+        out = []
+        for i in range(n):
+            m = int(ints[i, 3])
+            fr = np.zeros(m, np.int32); bx = np.zeros((m, 4), np.int32); sc = np.zeros(m, np.float64)
+            self.L.cvref_tbd_track_history(self.h, C.c_int(i), fr.ctypes.data_as(C.c_void_p), bx.ctypes.data_as(C.c_void_p),
+                                           sc.ctypes.data_as(C.c_void_p), C.c_int(m))
+            out.append((ints[i].copy(), dbl[i].copy(), fr, bx, sc))
+        return out
+
+    def reset(self):
+        self.L.cvref_tbd_reset(self.h)
+
+    def snapshot(self):
+        return self.L.cvref_tbd_snapshot(self.h)
+
+    def restore(self, s):
+        self.L.cvref_tbd_restore(self.h, C.c_int(s))
+
+    def metrics(self):
+        ints = np.zeros((4096, 5), np.int32); ov = np.zeros(4096, np.float64)
+        n = self.L.cvref_tbd_metrics(self.h, ints.ctypes.data_as(C.c_void_p), ov.ctypes.data_as(C.c_void_p), C.c_int(4096))
+        return ints[:n], ov[:n]
+
+
+def our_state(t):
+    out = []
+    for i, tr in enumerate(t.getTracks()):
+        ints = np.array([tr.id, tr.age, tr.totalVisibleCount, tr.historyLen, *tr.predPosition, *tr.bbox, tr.lastFrame], np.int32)
+        dbl = np.array([tr.maxConfidence, tr.avgConfidence, tr.bboxOverlap], np.float64)
+        fr, bx, sc = t.trackHistory(i)
+        out.append((ints, dbl, fr, bx, sc))
+    return out
+
+
+def same_state(a, b):
+    if len(a) != len(b):
+        return False
+    return all(all(np.array_equal(x, y, equal_nan=True) for x, y in zip(ta, tb)) for ta, tb in zip(a, b))
+
+
+def scene(seed, nframes, nobj, with_conf, W=1280, H=720, miss=0.15, clutter=1.0, jitter=3):
+    """Seeded detection sequences: objects on constant-velocity paths with box jitter, random misses, clutter boxes,
+    objects entering / leaving the window, crossing paths, frame gaps; confidences unknown (-1.0, as the sample passes
+    them) or uniform in [0, 1]."""
+    rng = np.random.RandomState(seed)
+    objs = []
+    for _ in range(nobj):
+        objs.append(dict(x=rng.uniform(-100, W), y=rng.uniform(0, H - 100), vx=rng.uniform(-12, 12), vy=rng.uniform(-4, 4),
+                         w=rng.randint(24, 120), t0=rng.randint(0, nframes // 2), t1=rng.randint(nframes // 2, nframes + 1)))
+    frames = []
+    f = 0
+    for k in range(nframes):
+        dets = []
+        for o in objs:
+            if not (o["t0"] <= k < o["t1"]) or rng.rand() < miss:
+                continue
+            w = int(o["w"] + rng.randint(-jitter, jitter + 1)); h = 2 * w + int(rng.randint(-jitter, jitter + 1))
+            x = int(round(o["x"] + o["vx"] * k + rng.randint(-jitter, jitter + 1))); y = int(round(o["y"] + o["vy"] * k + rng.randint(-jitter, jitter + 1)))
+            dets.append(tbd.Detection(-1, f, (x, y, max(w, 1), max(h, 1)), rng.rand() if with_conf else -1.0))
+        for _ in range(rng.poisson(clutter)):
+            w = int(rng.randint(16, 200))
+            dets.append(tbd.Detection(-1, f, (int(rng.randint(-50, W)), int(rng.randint(-50, H)), w, 2 * w), rng.rand() if with_conf else -1.0))
+        order = rng.permutation(len(dets))
+        frames.append((f, [dets[i] for i in order]))
+        f += 1 if rng.rand() < 0.9 else int(rng.randint(2, 4))       # occasional frame gaps
+    return frames
+
+
+ARGS = [
+    # the sample's defaults (samples/gpu/tbd.cpp: Args::Args) and variations that exercise the deletion rules
+    tbd.TbdArgs(10.0, 16, 4, 0.3, 0.2, 1),
+    tbd.TbdArgs(10.0, 4, 8, 0.6, -0.5, 1),
+    tbd.TbdArgs(0.5, 8, 2, 0.5, 0.35, 0),
+]
+
+needs_ref = pytest.mark.skipif(not os.path.exists(REF_SO), reason="oracle/_ref/libcvref.so not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("ai", range(len(ARGS)))
+@pytest.mark.parametrize("seed,nobj,with_conf", [(1, 3, False), (2, 8, True), (3, 15, True), (4, 25, False), (5, 0, True)])
+def test_tracks_identical_to_reference(ai, seed, nobj, with_conf):
+    a = ARGS[ai]
+    ours, ref = tbd.Tracker(a), RefTracker(a)
+    for f, dets in scene(seed, 60, nobj, with_conf):
+        ours.performTrackingStep(dets, f)
+        ref.step(dets, f)
+        assert same_state(our_state(ours), ref.state()), (seed, f)
+    if a.shouldStoreMetrics:
+        ri, ro = ref.metrics()
+        m = ours.metrics()
+        assert len(m) == len(ri) == 60
+        assert np.array_equal(ri, np.array([[x.truePositives, x.falseNegatives, x.falsePositives, x.groundTruths, x.numMatches] for x in m], np.int32))
+        assert np.array_equal(ro, np.array([x.bboxOverlap for x in m]))
+    else:
+        assert ours.metrics() == []
+
+
+@needs_ref
+def test_dense_crowd_assignment():
+    """Many overlapping boxes: ties and multi-pass zero covering in the assignment procedure."""
+    a = tbd.TbdArgs(10.0, 16, 4, 0.3, -1.0, 1)
+    ours, ref = tbd.Tracker(a), RefTracker(a)
+    for f, dets in scene(77, 40, 60, True, miss=0.3, clutter=6.0, jitter=9):
+        ours.performTrackingStep(dets, f)
+        ref.step(dets, f)
+        assert same_state(our_state(ours), ref.state()), f
+    # identical boxes in consecutive frames: exact zeros and ties everywhere
+    ours.reset(); ref.reset()
+    grid = [tbd.Detection(-1, 0, (40 * i, 30 * j, 64, 128), 0.9) for i in range(6) for j in range(4)]
+    for f in range(6):
+        dets = [tbd.Detection(-1, f, (d.x, d.y, d.width, d.height), 0.9) for d in grid]
+        ours.performTrackingStep(dets, f)
+        ref.step(dets, f)
+        assert same_state(our_state(ours), ref.state()), f
+
+
+@needs_ref
+def test_history_age_replay_like_the_sample():
+    """samples/gpu/tbd.cpp:642-680: every step restarts from the track set of `historyAge` frames ago."""
+    a = ARGS[0]
+    ours, ref = tbd.Tracker(a), RefTracker(a)
+    rng = np.random.RandomState(9)
+    ours_buf, ref_buf = {}, {}
+    for k, (f, dets) in enumerate(scene(21, 50, 10, True)):
+        age = int(rng.randint(1, 4))
+        if k >= age:
+            ours.setTracks(ours_buf[k - age]); ref.restore(ref_buf[k - age])
+        else:
+            ours.setTracks(None); ref.restore(-1)
+        ours.performTrackingStep(dets, f)
+        ref.step(dets, f)
+        assert same_state(our_state(ours), ref.state()), k
+        ours_buf[k] = ours.copyTracks(); ref_buf[k] = ref.snapshot()
+
+
+def test_reports_track_of_each_detection_and_bounds():
+    a = tbd.TbdArgs(10.0, 16, 4, 0.3, -1.0, 1)
+    t = tbd.Tracker(a)
+    d0 = [tbd.Detection(-1, 0, (100, 100, 64, 128), 0.9), tbd.Detection(-1, 0, (600, 300, 64, 128), 0.8)]
+    assert list(t.performTrackingStep(d0, 0)) == [-1, -1]
+    d1 = [tbd.Detection(-1, 1, (604, 302, 64, 128), 0.8), tbd.Detection(-1, 1, (104, 100, 64, 128), 0.9)]
+    assert list(t.performTrackingStep(d1, 1)) == [1, 0]
+    assert [tr.id for tr in t.getTracks()] == [0, 1]
+    # a track predicted beyond the window is dropped before assignment (tbd.cpp:319-344; default window 1280x720)
+    t.reset()
+    t.performTrackingStep([tbd.Detection(-1, 0, (1200, 100, 64, 128), 0.9)], 0)
+    t.performTrackingStep([tbd.Detection(-1, 1, (1260, 100, 64, 128), 0.9)], 1)
+    assert len(t.getTracks()) == 1
+    assert list(t.performTrackingStep([], 2)) == [] and len(t.getTracks()) == 0      # predicted x = 1320 >= 1280
+    assert tbd.computeBoundingBoxOverlap((0, 0, 10, 10), (5, 0, 10, 10)) == pytest.approx(50.0 / 150.0)
+    assert tbd.computeBoundingBoxOverlap((0, 0, 10, 10), (20, 20, 5, 5)) == 0.0
+    with pytest.raises(Exception):
+        t.trackHistory(5)
+
+
+def test_golden_sequence():
+    """The fixture recorded from the unmodified reference (travels to machines without /root/reference)."""
+    g = np.load(GOLDEN)
+    a = tbd.TbdArgs(*[float(x) if i in (0, 3, 4) else int(x) for i, x in enumerate(g["args"])])
+    t = tbd.Tracker(a)
+    frames = scene(int(g["seed"]), int(g["nframes"]), int(g["nobj"]), True)
+    for k, (f, dets) in enumerate(frames):
+        t.performTrackingStep(dets, f)
+        st = our_state(t)
+        ints = np.array([s[0] for s in st], np.int32).reshape(-1, 13)
+        dbl = np.array([s[1] for s in st], np.float64).reshape(-1, 3)
+        assert np.array_equal(ints, g["ints_%d" % k]) and np.array_equal(dbl, g["dbl_%d" % k]), k

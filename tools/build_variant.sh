@@ -5,8 +5,8 @@ set -e
 cd "$(dirname "$0")/.."
 name=$1; shift
 mkdir -p build_variants/$name
-for f in resize hist svm hog_host hog_storage; do
-  /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-O2 "$@" -c opencv_b200/csrc/$f.cu -o build_variants/$name/$f.o &
+for f in resize.cu hist.cu svm.cu hog_host.cu hog_storage.cu tbd_host.cpp; do
+  /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-O2 "$@" -c opencv_b200/csrc/$f -o build_variants/$name/${f%.*}.o &
 done
 wait
 /usr/local/cuda/bin/nvcc -shared -o build_variants/libhogb200_$name.so build_variants/$name/*.o -Xcompiler -fPIC -cudart static
