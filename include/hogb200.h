@@ -158,6 +158,12 @@ int hogb200_window_scores(hogb200_t* h, int slot, const hogb200_image* img, floa
                           int* wins_x, int* wins_y);
 /* cv::groupRectangles(rects, group_threshold, eps) (objdetect/src/cascadedetect.cpp:64-174, 366-371), in place */
 int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold, double eps, size_t* count);
+/* The same function computed on the handle's device (csrc/group.cu: sort by x, warp-per-rect SimilarRects sweep,
+ * lock-free union-find, class sums, filter, ordered compaction): identical output, for candidate lists of tens of
+ * thousands of rects.  detectMultiScale switches to it by itself from 1024 candidates
+ * per frame (environment HOGB200_GPU_GROUP_MIN overrides, 0 = never). */
+int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n, int group_threshold, double eps,
+                                    size_t* count);
 
 /* ---- instrumentation for bench.py: device time (ms, CUDA events on the handle's stream) of the stages of
  * the last work call, and the number of kernels it launched. */

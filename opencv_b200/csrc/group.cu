@@ -1,0 +1,229 @@
+// group.cu -- cv::groupRectangles(rects, groupThreshold, eps) on the device.
+//
+// Reference: modules/objdetect/src/cascadedetect.cpp:64-174 (grouping), core/operations.hpp:481-569 (cv::partition),
+// objdetect.hpp:121-134 (SimilarRects).  The host version in hog_host.cu stays the default for the handful of hits
+// a frame normally has; this one takes over when a frame yields tens of thousands of candidates (low hit threshold,
+// dense pyramids), where the pairwise predicate dominates the frame time on the host.
+//
+// Same result, bit for bit, as the reference on the same input order:
+//   * classes = connected components of SimilarRects; cv::partition numbers them by first appearance, i.e. by the
+//     smallest member index.  Here: lock-free union-find whose hooking always puts the larger root under the
+//     smaller one, so a root IS the smallest member; an exclusive scan over the root flags gives the class number.
+//   * candidate pairs: rects sorted by x (CUB radix sort, the one library call -- a sort is not the subject here);
+//     a warp owns one rect and sweeps the sorted order to the right while x_b - x_a <= eps (w_a + h_a) / 2, which
+//     bounds SimilarRects' own delta from above (the host's sweep, hog_host.cu group_rectangles).
+//   * class sums in int32 atomics (order-free, exact), mean with float s = 1.f / n and round-half-even, the
+//     "inside a stronger class" filter per class against all classes, ordered compaction by a second scan.
+#include "hog_internal.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+namespace hogk {
+
+namespace {
+
+struct RectI { int x, y, w, h; };
+
+__global__ void iota_keys_kernel(const RectI* __restrict__ r, int n, int* __restrict__ keys, int* __restrict__ idx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { keys[i] = r[i].x; idx[i] = i; }
+}
+
+__global__ void gather_kernel(const RectI* __restrict__ r, const int* __restrict__ idx, int n, RectI* __restrict__ sorted,
+                              int* __restrict__ parent)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { sorted[i] = r[idx[i]]; parent[i] = i; }
+}
+
+__device__ __forceinline__ int uf_find(int* parent, int a)
+{
+    // parents only ever decrease, so reading a stale one is harmless; halve the path on the way up
+    int p = ((volatile int*)parent)[a];
+    while (p != a) {
+        const int g = ((volatile int*)parent)[p];
+        if (g != p) atomicMin(&parent[a], g);
+        a = p; p = g;
+    }
+    return a;
+}
+
+__device__ __forceinline__ void uf_unite(int* parent, int a, int b)
+{
+    for (;;) {
+        a = uf_find(parent, a); b = uf_find(parent, b);
+        if (a == b) return;
+        if (a > b) { const int t = a; a = b; b = t; }
+        if (atomicCAS(&parent[b], b, a) == b) return;      // b was still a root: now under the smaller root a
+    }
+}
+
+// SimilarRects::operator() (objdetect.hpp:126-133), double arithmetic as in the reference
+__device__ __forceinline__ bool similar(const RectI& r1, const RectI& r2, double eps)
+{
+    const double delta = eps * (min(r1.w, r2.w) + min(r1.h, r2.h)) * 0.5;
+    return abs(r1.x - r2.x) <= delta && abs(r1.y - r2.y) <= delta &&
+           abs(r1.x + r1.w - r2.x - r2.w) <= delta && abs(r1.y + r1.h - r2.y - r2.h) <= delta;
+}
+
+// one warp per rect (sorted position a): lanes test positions a+1+lane, a+33+lane, ... until all are out of reach
+__global__ void __launch_bounds__(256) unite_kernel(const RectI* __restrict__ sorted, const int* __restrict__ idx, int n,
+                                                    double eps, int* __restrict__ parent)
+{
+    const int lane = threadIdx.x & 31;
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= n) return;
+    const RectI ra = sorted[a];
+    const int ia = idx[a];
+    const double reach = eps * (ra.w + ra.h) * 0.5;
+    for (int b = a + 1 + lane; ; b += 32) {
+        bool in_reach = false;
+        if (b < n) {
+            const RectI rb = sorted[b];
+            in_reach = rb.x - ra.x <= reach;
+            if (in_reach && similar(ra, rb, eps)) uf_unite(parent, ia, idx[b]);
+        }
+        if (!__any_sync(0xffffffffu, in_reach)) break;       // sorted by x: nothing further right can be in reach
+    }
+}
+
+__global__ void root_flags_kernel(int* __restrict__ parent, int n, int* __restrict__ root_of, int* __restrict__ is_root)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const int r = uf_find(parent, i);
+        root_of[i] = r;
+        is_root[i] = r == i;
+    }
+}
+
+// exclusive scan of n ints by ONE CTA of 1024 threads (n is at most a few million and this runs twice per call)
+__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ in, int* __restrict__ out, int n, int* __restrict__ total)
+{
+    __shared__ int part[1024];
+    const int t = threadIdx.x, per = (n + 1023) / 1024;
+    const int b = min(n, t * per), e = min(n, b + per);
+    int s = 0;
+    for (int i = b; i < e; i++) s += in[i];
+    part[t] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const int v = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    int off = part[t] - s;
+    for (int i = b; i < e; i++) { const int v = in[i]; out[i] = off; off += v; }
+    if (t == 1023) *total = part[1023];
+}
+
+// rrects[cls] += rect, rweights[cls]++ (cascadedetect.cpp:86-95); sums = 5 ints per class (x, y, w, h, count)
+__global__ void accumulate_kernel(const RectI* __restrict__ r, const int* __restrict__ root_of, const int* __restrict__ class_of_root,
+                                  int n, int* __restrict__ sums)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        int* s = sums + 5 * class_of_root[root_of[i]];
+        atomicAdd(s + 0, r[i].x); atomicAdd(s + 1, r[i].y); atomicAdd(s + 2, r[i].w); atomicAdd(s + 3, r[i].h);
+        atomicAdd(s + 4, 1);
+    }
+}
+
+// mean rect of a class: Rect(saturate_cast<int>(r.x * s), ...) with float s = 1.f / n (cascadedetect.cpp:97-106)
+__device__ __forceinline__ RectI class_mean(const int* __restrict__ s)
+{
+    const float f = 1.f / (float)s[4];
+    return RectI{__float2int_rn((float)s[0] * f), __float2int_rn((float)s[1] * f), __float2int_rn((float)s[2] * f),
+                 __float2int_rn((float)s[3] * f)};
+}
+
+// keep class i unless it is too weak or sits inside a stronger class (cascadedetect.cpp:112-161)
+__global__ void filter_kernel(const int* __restrict__ sums, int nclasses, int thr, double eps, int* __restrict__ keep,
+                              RectI* __restrict__ mean)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nclasses) return;
+    const int n1 = sums[5 * i + 4];
+    const RectI r1 = class_mean(sums + 5 * i);
+    mean[i] = r1;
+    int k = n1 > thr;
+    for (int j = 0; k && j < nclasses; j++) {
+        const int n2 = sums[5 * j + 4];
+        if (j == i || n2 <= thr) continue;
+        const RectI r2 = class_mean(sums + 5 * j);
+        const int dx = __double2int_rn(r2.w * eps), dy = __double2int_rn(r2.h * eps);
+        if (r1.x >= r2.x - dx && r1.y >= r2.y - dy && r1.x + r1.w <= r2.x + r2.w + dx && r1.y + r1.h <= r2.y + r2.h + dy &&
+            (n2 > max(3, n1) || n1 < 3))
+            k = 0;
+    }
+    keep[i] = k;
+}
+
+__global__ void emit_kernel(const RectI* __restrict__ mean, const int* __restrict__ keep, const int* __restrict__ pos, int nclasses,
+                            RectI* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nclasses && keep[i]) out[pos[i]] = mean[i];
+}
+
+inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+}  // namespace
+
+size_t group_workspace_bytes(int n)
+{
+    size_t sort_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
+    // rects, sorted rects, means, out: 4 x 16 n;  keys x2, idx x2, parent, root_of, flags, scan, keep, pos: 10 x 4 n;
+    // sums 20 n; counters
+    return 4 * align256((size_t)16 * n) + 10 * align256((size_t)4 * n) + align256((size_t)20 * n) + align256(sort_bytes) + 512;
+}
+
+// rects (host, reference order) -> grouped rects (host).  ws: device workspace of group_workspace_bytes(n).
+// Returns the number of output rects, or -1 on a CUDA error.
+int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int* h_out, void* ws, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    unsigned char* p = (unsigned char*)ws;
+    auto take = [&](size_t bytes) { void* r = p; p += align256(bytes); return r; };
+    RectI* d_rects = (RectI*)take((size_t)16 * n); RectI* d_sorted = (RectI*)take((size_t)16 * n);
+    RectI* d_mean = (RectI*)take((size_t)16 * n); RectI* d_out = (RectI*)take((size_t)16 * n);
+    int* d_keys = (int*)take((size_t)4 * n); int* d_keys2 = (int*)take((size_t)4 * n);
+    int* d_idx = (int*)take((size_t)4 * n); int* d_idx2 = (int*)take((size_t)4 * n);
+    int* d_parent = (int*)take((size_t)4 * n); int* d_root = (int*)take((size_t)4 * n);
+    int* d_flag = (int*)take((size_t)4 * n); int* d_scan = (int*)take((size_t)4 * n);
+    int* d_keep = (int*)take((size_t)4 * n); int* d_pos = (int*)take((size_t)4 * n);
+    int* d_sums = (int*)take((size_t)20 * n);
+    int* d_cnt = (int*)take(512);
+    size_t sort_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
+    void* d_sort = take(sort_bytes);
+
+    const int T = 256, B = (n + T - 1) / T;
+    cudaMemcpyAsync(d_rects, h_rects, (size_t)16 * n, cudaMemcpyHostToDevice, st);
+    iota_keys_kernel<<<B, T, 0, st>>>(d_rects, n, d_keys, d_idx);
+    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_keys, d_keys2, d_idx, d_idx2, n, 0, 32, st);
+    gather_kernel<<<B, T, 0, st>>>(d_rects, d_idx2, n, d_sorted, d_parent);
+    unite_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_idx2, n, eps, d_parent);
+    root_flags_kernel<<<B, T, 0, st>>>(d_parent, n, d_root, d_flag);
+    scan_kernel<<<1, 1024, 0, st>>>(d_flag, d_scan, n, d_cnt);
+    int nclasses = 0;
+    cudaMemcpyAsync(&nclasses, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemsetAsync(d_sums, 0, (size_t)20 * n, st);
+    accumulate_kernel<<<B, T, 0, st>>>(d_rects, d_root, d_scan, n, d_sums);
+    if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
+    const int BC = (nclasses + T - 1) / T;
+    filter_kernel<<<BC, T, 0, st>>>(d_sums, nclasses, thr, eps, d_keep, d_mean);
+    scan_kernel<<<1, 1024, 0, st>>>(d_keep, d_pos, nclasses, d_cnt + 1);
+    emit_kernel<<<BC, T, 0, st>>>(d_mean, d_keep, d_pos, nclasses, d_out);
+    int nout = 0;
+    cudaMemcpyAsync(&nout, d_cnt + 1, sizeof(int), cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
+    if (nout > 0) cudaMemcpyAsync(h_out, d_out, (size_t)16 * nout, cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) return -1;
+    return nout;
+}
+
+}  // namespace hogk

@@ -119,6 +119,7 @@ struct hogb200 {
     size_t cand_cap = 0;
     PinBuf<unsigned char> h_cand;
     DevBuf<float> d_desc;
+    DevBuf<unsigned char> d_group;  // workspace of the device groupRectangles (group.cu)
     Plan plan, plan1, plan_grp;     // multi-scale plan, single-scale plan, multi-scale plan of the batch path (frame groups)
     // timing
     int timing = 0; cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -577,8 +578,40 @@ void group_rectangles(std::vector<hogb200_rect>& rects, int groupThreshold, doub
     }
 }
 
+// cv::groupRectangles on the device (group.cu): same classes, same order, same rects as group_rectangles above
+int group_rectangles_device(hogb200* h, std::vector<hogb200_rect>& rects, int groupThreshold, double eps)
+{
+    if (groupThreshold <= 0 || rects.empty()) return HOGB200_OK;
+    const int n = (int)rects.size();
+    CK(cudaSetDevice(h->device));
+    CK(h->d_group.reserve(hogk::group_workspace_bytes(n)));
+    std::vector<hogb200_rect> out(n);
+    const int m = hogk::group_rectangles_device(&rects[0].x, n, groupThreshold, eps, &out[0].x, h->d_group.p, h->stream);
+    if (m < 0) return fail(HOGB200_CUDA_ERROR, std::string("groupRectangles on the device: ") + cudaGetErrorString(cudaGetLastError()));
+    out.resize(m);
+    rects.swap(out);
+    return HOGB200_OK;
+}
+
+// frames with this many candidates or more are grouped on the device (HOGB200_GPU_GROUP_MIN overrides; 0 = never)
+size_t gpu_group_min()
+{
+    static const size_t v = [] {
+        const char* e = getenv("HOGB200_GPU_GROUP_MIN");
+        return e ? (size_t)atoll(e) : (size_t)1024;
+    }();
+    return v;
+}
+
+void group_rectangles_auto(hogb200* h, std::vector<hogb200_rect>& rects, int groupThreshold, double eps)
+{
+    if (gpu_group_min() > 0 && rects.size() >= gpu_group_min() && group_rectangles_device(h, rects, groupThreshold, eps) == HOGB200_OK)
+        return;
+    group_rectangles(rects, groupThreshold, eps);
+}
+
 // candidates of one (frame, detector), already in (level, y, x) order -> rects (hog.cpp:471-481) [+ grouping :484-487]
-void candidates_to_rects(const hogb200* h, const Plan& P, const Candidate* c, size_t n,
+void candidates_to_rects(hogb200* h, const Plan& P, const Candidate* c, size_t n,
                          std::vector<hogb200_rect>& rects, std::vector<double>* conf)
 {
     rects.clear();
@@ -594,7 +627,7 @@ void candidates_to_rects(const hogb200* h, const Plan& P, const Candidate* c, si
         rects.push_back(r);
         if (conf) conf->push_back((double)c[i].score);
     }
-    if (h->group_threshold > 0) group_rectangles(rects, h->group_threshold, 0.2);
+    if (h->group_threshold > 0) group_rectangles_auto(h, rects, h->group_threshold, 0.2);
 }
 
 void finish_timing(hogb200* h, const Plan& P, int launches, size_t ncand)
@@ -678,7 +711,7 @@ void hogb200_destroy(hogb200_t* h)
     for (auto& b : h->d_frame) b.release();
     for (auto& b : h->d_raw) b.release();
     h->d_pyr.release(); h->d_hist.release();
-    h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release();
+    h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release(); h->d_group.release();
     for (Plan* P : {&h->plan, &h->plan1, &h->plan_grp}) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();
@@ -1036,6 +1069,19 @@ int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold,
     if (n && !rects) return fail(HOGB200_BAD_ARG, "null rects");
     std::vector<hogb200_rect> v(rects, rects + n);
     group_rectangles(v, group_threshold, eps);
+    if (!v.empty()) memcpy(rects, v.data(), v.size() * sizeof(hogb200_rect));
+    if (count) *count = v.size();
+    return HOGB200_OK;
+}
+
+int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n, int group_threshold, double eps, size_t* count)
+{
+    H_OR_FAIL;
+    if (n && !rects) return fail(HOGB200_BAD_ARG, "null rects");
+    if (n > (size_t)1 << 26) return fail(HOGB200_BAD_ARG, "too many rects");
+    std::vector<hogb200_rect> v(rects, rects + n);
+    const int rc = group_rectangles_device(h, v, group_threshold, eps);
+    if (rc) return rc;
     if (!v.empty()) memcpy(rects, v.data(), v.size() * sizeof(hogb200_rect));
     if (count) *count = v.size();
     return HOGB200_OK;

@@ -108,6 +108,11 @@ int svm_tile_cost(int cols_left, int rows_left);   // relative time of a tile wi
 void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_hist, int win_bx, int win_by,
                     int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);
 
+// cv::groupRectangles on the device (group.cu): rects are 4 ints (x, y, width, height) in host memory, in the
+// reference's input order; returns the number of grouped rects written to h_out, -1 on a CUDA error
+size_t group_workspace_bytes(int n);
+int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int* h_out, void* ws, cudaStream_t st);
+
 int hist_tile_blocks_x();   // blocks per tile in x (14)
 int hist_strip_blocks_y();  // block rows per strip: 0 = let the host choose, else the HOGB200_STRIP override
 

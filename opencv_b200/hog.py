@@ -98,6 +98,7 @@ def load_library():
     L.hogb200_window_scores.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Image), C.c_void_p, C.c_size_t,
                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.hogb200_group_rectangles.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
+    L.hogb200_group_rectangles_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
     L.hogb200_model_read.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_model_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t]
     L.hogb200_save.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]
@@ -364,4 +365,11 @@ class HOG:
         rc = L.hogb200_group_rectangles(r.ctypes.data, len(r), group_threshold, eps, C.byref(n))
         if rc:
             raise HogError(rc, L.hogb200_last_error().decode())
+        return r[:n.value].copy()
+
+    def groupRectanglesDevice(self, rects, group_threshold, eps=0.2):
+        """cv::groupRectangles computed on the device (csrc/group.cu): same output as groupRectangles."""
+        r = np.ascontiguousarray(np.asarray(rects, np.int32).reshape(-1, 4)).copy()
+        n = C.c_size_t()
+        self._ck(self._L.hogb200_group_rectangles_device(self._h, r.ctypes.data, len(r), group_threshold, eps, C.byref(n)))
         return r[:n.value].copy()

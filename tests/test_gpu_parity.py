@@ -461,3 +461,55 @@ def test_full_size_kitti_sequence_two_detectors(hog, port):
                 assert ok
     finally:
         hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+# ------------------------------------------------------------------ groupRectangles on the device (row f4)
+def _rect_cloud(seed, n, nclusters, W=1920, H=1080):
+    """Window-like rects (1:2) scattered around cluster centres at several scales, plus isolated ones, in random order."""
+    rng = np.random.RandomState(seed)
+    cx = rng.randint(0, W, nclusters); cy = rng.randint(0, H, nclusters); cw = rng.randint(40, 400, nclusters)
+    k = rng.randint(0, nclusters, n)
+    w = np.maximum(8, (cw[k] * rng.uniform(0.8, 1.25, n)).astype(np.int32))
+    jit = np.maximum(1, cw[k] // 6)
+    x = cx[k] + rng.randint(-1, 2, n) * rng.randint(0, 1 << 30, n) % jit
+    y = cy[k] + rng.randint(-1, 2, n) * rng.randint(0, 1 << 30, n) % jit
+    r = np.stack([x, y, w, 2 * w], 1).astype(np.int32)
+    lone = rng.rand(n) < 0.05
+    r[lone, 0] = rng.randint(0, W, lone.sum()); r[lone, 1] = rng.randint(0, H, lone.sum())
+    return r
+
+
+@pytest.mark.parametrize("n,nclusters", [(1, 1), (40, 3), (3000, 40), (50000, 300)])
+def test_group_rectangles_device_equals_host(hog, n, nclusters):
+    """Bit-identical rects in identical order: device union-find grouping vs the host restatement of
+    cv::groupRectangles (itself pinned to the unmodified reference in tests/test_oracle_vs_ref.py / test_cabi_cpu.py)."""
+    from opencv_b200 import HOG
+    r = _rect_cloud(n, n, nclusters)
+    for thr in (1, 2, 5):
+        for eps in (0.2, 0.5):
+            want = HOG.groupRectangles(r, thr, eps)
+            got = hog.groupRectanglesDevice(r, thr, eps)
+            assert np.array_equal(got, want), (n, thr, eps, len(got), len(want))
+    assert len(hog.groupRectanglesDevice(np.zeros((0, 4), np.int32), 2)) == 0
+    assert np.array_equal(hog.groupRectanglesDevice(r, 0), r)          # threshold <= 0: untouched (cascadedetect.cpp:66-75)
+
+
+def test_group_rectangles_device_vs_reference():
+    """Against the unmodified cv::groupRectangles directly."""
+    from opencv_b200 import HOG
+    h = HOG.create()
+    ref = Ref()
+    r = _rect_cloud(5, 20000, 150)
+    assert np.array_equal(h.groupRectanglesDevice(r, 2, 0.2), ref.group_rectangles(r, 2, 0.2))
+
+
+def test_dense_hits_grouped_on_device(hog, port):
+    """A low hit threshold with grouping on: thousands of candidates per frame take the device grouping path inside
+    detectMultiScale (>= 1024 candidates) and must give the oracle's grouped set."""
+    img = synthetic_frame(321, 800, 600, 4, silhouettes=6)
+    det = hog.getDefaultPeopleDetector()
+    hog.setHitThreshold(-3.0); hog.setGroupThreshold(0)
+    assert len(hog.detectMultiScale(img)) >= 2048
+    ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, -3.0, 2)
+    assert ok and len(exp) > 0
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
