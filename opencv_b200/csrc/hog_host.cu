@@ -121,6 +121,7 @@ struct hogb200 {
     DevBuf<float> d_desc;
     DevBuf<unsigned char> d_group;  // workspace of the device groupRectangles (group.cu)
     Plan plan, plan1, plan_grp;     // multi-scale plan, single-scale plan, multi-scale plan of the batch path (frame groups)
+    Plan plan_part[kMaxGroup];      // batch path: plans sized for the smaller groups (lead-in, ragged last group)
     // timing
     int timing = 0; cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     hogb200_timings last = {};
@@ -712,7 +713,9 @@ void hogb200_destroy(hogb200_t* h)
     for (auto& b : h->d_raw) b.release();
     h->d_pyr.release(); h->d_hist.release();
     h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release(); h->d_group.release();
-    for (Plan* P : {&h->plan, &h->plan1, &h->plan_grp}) {
+    std::vector<Plan*> plans = {&h->plan, &h->plan1, &h->plan_grp};
+    for (Plan& P : h->plan_part) plans.push_back(&P);
+    for (Plan* P : plans) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();
     }
@@ -829,6 +832,13 @@ int check_work_params(const hogb200* h)
     if (h->win_stride_x % h->g.block_stride_w != 0 || h->win_stride_y % h->g.block_stride_h != 0)
         return fail(HOGB200_BAD_ARG, "win_stride must be a multiple of block_stride (hog.cpp:341)");
     return HOGB200_OK;
+}
+
+// first group of a batch of host frames = one frame (HOGB200_LEAD_IN=0 disables)
+bool batch_lead_in()
+{
+    static const bool v = [] { const char* e = getenv("HOGB200_LEAD_IN"); return !e || atoi(e) != 0; }();
+    return v;
 }
 
 // frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup)
@@ -970,17 +980,27 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, grp))) return rc;
         Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
+        static const bool trace = getenv("HOGB200_TRACE") != nullptr;      // debugging aid: per-group timeline on stderr
+        cudaEvent_t tev[kChunk][4]; int ntev = 0;
         for (int attempt = 0; attempt < 2; attempt++) {
             if ((rc = ensure_cand(h, cap))) return rc;
             CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
-            for (int g0 = 0, gi = 0; g0 < nf; g0 += grp, gi++) {
-                const int ng = std::min(grp, nf - g0);
+            // Nothing hides the upload of the first group, so when frames come from host memory the batch opens with
+            // groups of 1 and grp - 1 frames: the kernels start after one frame's copy instead of a whole group's,
+            // and the copies (faster than the kernels per frame) stay ahead from then on.
+            bool lead_in = false;
+            for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
+            lead_in = lead_in && nf > grp && batch_lead_in();
+            for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
+                ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
                 const int b = gi & 1;                     // double-buffered staging, per group
                 FrameRef f[kMaxGroup];
                 bool any_host = false;
                 for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
                 if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
                 else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
+                if (trace) { cudaEventCreate(&tev[gi][0]); cudaEventCreate(&tev[gi][1]); cudaEventCreate(&tev[gi][2]); cudaEventCreate(&tev[gi][3]);
+                             cudaEventRecord(tev[gi][0], any_host ? cs : st); }
                 for (int j = 0; j < ng; j++) {
                     const hogb200_image* im = fr + g0 + j;
                     // host frames: upload on the copy stream, overlapping the previous group's kernels
@@ -990,11 +1010,31 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
                     CK(cudaEventRecord(h->up_done[b], cs));
                     CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
                 }
-                if ((rc = queue_group(h, P, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches))) return rc;
+                if (trace) { cudaEventRecord(tev[gi][1], any_host ? cs : st); cudaEventRecord(tev[gi][2], st); }
+                // a group smaller than grp runs on a plan of its own size: work lists dealt for grp frames leave the
+                // persistent kernels unbalanced when most of their items belong to absent frames
+                Plan* Pg = &P;
+                if (ng != grp) {
+                    Pg = &h->plan_part[ng];
+                    if ((rc = build_plan(h, *Pg, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, ng))) return rc;
+                }
+                if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches))) return rc;
                 CK(cudaEventRecord(h->fr_done[b], st));
+                if (trace) { cudaEventRecord(tev[gi][3], st); ntev = gi + 1; }
             }
             size_t n = 0;
             rc = fetch_candidates(h, c, &n);
+            if (trace) {
+                cudaDeviceSynchronize();
+                for (int gi = 0; gi < ntev; gi++) {
+                    float a = -1, b2 = -1, c2 = -1, d = -1;
+                    cudaError_t e1 = cudaEventElapsedTime(&a, tev[0][0], tev[gi][0]); cudaEventElapsedTime(&b2, tev[0][0], tev[gi][1]);
+                    cudaEventElapsedTime(&c2, tev[0][0], tev[gi][2]); cudaEventElapsedTime(&d, tev[0][0], tev[gi][3]);
+                    if (e1 != cudaSuccess) fprintf(stderr, "(%s) ", cudaGetErrorString(e1));
+                    fprintf(stderr, "group %2d: upload %.3f .. %.3f   kernels %.3f .. %.3f\n", gi, a, b2, c2, d);
+                }
+                for (int gi = 0; gi < ntev; gi++) for (int k = 0; k < 4; k++) cudaEventDestroy(tev[gi][k]);
+            }
             if (rc == HOGB200_CAPACITY && attempt == 0) { cap = (size_t)P.nwindows * nslots * nf + 16; continue; }
             if (rc) return rc;
             break;
