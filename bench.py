@@ -28,6 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, CN = 1920, 1080, 4
 NLEVELS, SCALE0, HIT, GROUP = 64, 1.05, 0.0, 2
+NSLOTS = 1
 BATCH = 32                       # frames per step per GPU: 32 x 8.3 MB = 265 MB of distinct input > 126 MB L2
 METRIC = "HOG detectMultiScale frames/s at 1080p"
 UNIT = "frames/s"
@@ -36,6 +37,40 @@ CONFIG = {"workload": "cv::cuda::HOG people detector, synthetic 1920x1080 8UC4, 
           "frames_per_step_per_gpu": BATCH, "levels": 44, "pyramid_pixels": 21995553, "windows": 261558,
           "parallelism": "frame-sharded (frame g -> rank g % N), no collective on the data path, host gather of boxes",
           "l2": "inputs larger than L2 (32 distinct frames = 265 MB per step per GPU)"}
+
+# The driver's line is the default workload (BASELINE.json's metric is quoted on configs[1]).  north_star also asks for
+# frames/s "on synthetic frames of each named shape": --workload selects the other BASELINE configs; the line keeps the
+# same keys, `metric` names the shape.  (shape, channels, nlevels, scale, hit, group, detectors, frames per step per GPU)
+WORKLOADS = {
+    "1080p": None,
+    "vga": dict(W=640, H=480, CN=1, NLEVELS=64, SCALE0=1.05, HIT=0.0, GROUP=2, NSLOTS=1, BATCH=512,
+                name="cv::HOGDescriptor default people detector, synthetic 640x480 8UC1, nlevels=64, scale 1.05, hit 0, "
+                     "group 2 (BASELINE configs[0])", metric="HOG detectMultiScale frames/s at 640x480 8UC1"),
+    "kitti": dict(W=1242, H=375, CN=4, NLEVELS=64, SCALE0=1.05, HIT=0.0, GROUP=2, NSLOTS=2, BATCH=128,
+                  name="example_gpu_tbd-style 1242x375 8UC4 sequence, pedestrian + (synthetic) vehicle detector scored in "
+                       "one pass, nlevels=64, scale 1.05, hit 0, group 2 (BASELINE configs[2])",
+                  metric="HOG detectMultiScale frames/s at 1242x375, two detectors"),
+    "4k": dict(W=3840, H=2160, CN=4, NLEVELS=64, SCALE0=1.05, HIT=0.0, GROUP=2, NSLOTS=1, BATCH=64,
+               name="synthetic 3840x2160 8UC4 frame stream, 64 frames per GPU per step (512 at 8 GPUs), nlevels=64, "
+                    "scale 1.05, hit 0, group 2 (BASELINE configs[3])", metric="HOG detectMultiScale frames/s at 3840x2160"),
+    "dense": dict(W=1920, H=1080, CN=4, NLEVELS=128, SCALE0=1.02, HIT=0.0, GROUP=0, NSLOTS=1, BATCH=32,
+                  name="dense-pyramid stress: synthetic 1920x1080 8UC4, scale 1.02, nlevels=128, hit 0, group 0 "
+                       "(BASELINE configs[4])", metric="HOG detectMultiScale frames/s at 1080p, scale 1.02 / 128 levels"),
+}
+
+
+def select_workload(name):
+    w = WORKLOADS[name]
+    if w is None:
+        return
+    g = globals()
+    for k in ("W", "H", "CN", "NLEVELS", "SCALE0", "HIT", "GROUP", "NSLOTS", "BATCH"):
+        g[k] = w[k]
+    g["METRIC"] = w["metric"]
+    mb = w["BATCH"] * w["W"] * w["H"] * w["CN"] / 1e6
+    g["CONFIG"] = {"workload": w["name"], "frames_per_step_per_gpu": w["BATCH"],
+                   "parallelism": CONFIG["parallelism"],
+                   "l2": "inputs larger than L2 (%d distinct frames = %.0f MB per step per GPU)" % (w["BATCH"], mb)}
 
 
 def make_frames(n, seed0):
@@ -103,8 +138,9 @@ def cpu_reference_fps(frames, nthreads=None):
         t = []
         for f in frames:
             t0 = time.perf_counter()
-            ref.detect_multiscale_stock(f, det, hit_threshold=HIT, win_stride=(8, 8), scale0=SCALE0, nlevels=NLEVELS,
-                                        final_threshold=float(GROUP))
+            for _ in range(NSLOTS):                   # one stock detector object per SVM model
+                ref.detect_multiscale_stock(f, det, hit_threshold=HIT, win_stride=(8, 8), scale0=SCALE0, nlevels=NLEVELS,
+                                            final_threshold=float(GROUP))
             t.append(time.perf_counter() - t0)
         return {"kind": "reference", "cores": cores, "times": t}
     port = Port()
@@ -136,7 +172,7 @@ def run_reference(args, rank):
                            note="stock cv::HOGDescriptor::detectMultiScale (CPU, BGR view of the same BGRA frames), "
                                 "1 frame per step"),
             "cpu_baseline": {"value": fps, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                             "sample": "%d x 1 frame 1920x1080, %s threads (OpenMP parallel_for_ over levels)" % (args.steps, r["cores"])},
+                             "sample": "%d x 1 frame %dx%d, %s threads (OpenMP parallel_for_ over levels)" % (args.steps, W, H, r["cores"])},
             "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -148,7 +184,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS), help="BASELINE config (default: the metric's)")
     args = ap.parse_args()
+    select_workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     rank = int(os.environ.get("RANK", "0")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -172,6 +210,9 @@ def main():
 
     hog = HOG.create(device=local_rank)
     hog.setSVMDetector(hog.getDefaultPeopleDetector())
+    if NSLOTS > 1:       # the reference ships no vehicle model: fixed-seed stand-in, same geometry
+        veh = hog.getDefaultPeopleDetector() + 0.02 * np.random.RandomState(3).standard_normal(3781).astype(np.float32)
+        hog.setSVMDetector(veh.astype(np.float32), 1)
     hog.setNumLevels(NLEVELS); hog.setScaleFactor(SCALE0); hog.setHitThreshold(HIT); hog.setGroupThreshold(GROUP)
     stream = torch.cuda.Stream()
     hog.setStream(stream.cuda_stream)
@@ -198,7 +239,9 @@ def main():
         with torch.cuda.stream(stream):
             e0.record(stream)
             for _ in range(steps):
-                out = hog.detectMultiScaleBatch(frames)
+                out = hog.detectMultiScaleBatch(frames, nslots=NSLOTS, capacity=1 << 20)
+                if NSLOTS > 1:                             # one list per frame: its detectors' boxes together
+                    out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(frames))]
                 nrects += sum(len(o) for o in out)
                 t = hog.lastTimings(); launches += t["kernel_launches"]; cands += t["candidates"]
                 if gather and world > 1:                   # boxes of all ranks -> rank 0, frame order, on the host
@@ -235,11 +278,11 @@ def main():
     # The timed region above issues one launch of each kernel per GROUP of frames (4 by default), so the roofline
     # launch is a group launch; the single-frame launch (latency path) is reported next to it.
     hog.enableTiming(True)
-    group = int(os.environ.get("HOGB200_GROUP", "4"))
+    group = hog.batchGroup(W, H, CN)      # frames per launch: the library's choice for this shape (HOGB200_GROUP forces)
     ks = {"resize_ms": [], "hist_ms": [], "svm_ms": [], "total_ms": []}
     ks1 = {"resize_ms": [], "hist_ms": [], "svm_ms": [], "total_ms": []}
     for i in range(3 + 12):
-        hog.detectMultiScaleBatch([dev[(i * group + j) % BATCH] for j in range(group)])
+        hog.detectMultiScaleBatch([dev[(i * group + j) % BATCH] for j in range(group)], nslots=NSLOTS, capacity=1 << 20)
         t = hog.lastTimings()
         hog.detectMultiScale(dev[i % BATCH])
         t1 = hog.lastTimings()
@@ -267,7 +310,10 @@ def main():
         util = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json"))).get("ncu", {})
     except Exception:
         pass
-    roofline = {"kernel": "hist_kernel<4> (fused gradient + histogram + L2-Hys, all 44 levels of %d frames in one launch)" % group,
+    CONFIG.update(levels=len(hog.levels(W, H)[0]), pyramid_pixels=int(tinfo["pyramid_pixels"]), windows=int(tinfo["windows"]))
+    if args.workload != "1080p":
+        traffic, util = None, {}          # the committed ncu capture is of the 1080p launch
+    roofline = {"kernel": "hist_kernel<%d> (fused gradient + histogram + L2-Hys, all %d levels of %d frames in one launch)" % (CN, CONFIG["levels"], group),
                 "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "limiter": "instruction issue + shared-memory bandwidth (DESIGN.md 4.1), not HBM",
                 "ncu": util, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
@@ -285,11 +331,12 @@ def main():
 
     if rank == 0 and world == 1 and not args.no_cpu:
         r = cpu_reference_fps([host[0]])                      # warm-up
-        r = cpu_reference_fps([host[i % BATCH] for i in range(8)])
+        r = cpu_reference_fps([host[i % BATCH] for i in range(8 if W * H < 4000000 else 4)])
         total = sum(r["times"])
         line["cpu_baseline"] = {"value": len(r["times"]) / total, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                                "sample": "8 frames 1920x1080 of the same workload, stock cv::HOGDescriptor::detectMultiScale, "
-                                          "best frame %.1f ms" % (1e3 * min(r["times"]))}
+                                "sample": "%d frames %dx%d of the same workload, stock cv::HOGDescriptor::detectMultiScale%s, "
+                                          "best frame %.1f ms" % (len(r["times"]), W, H, " (once per detector)" if NSLOTS > 1 else "",
+                                                                  1e3 * min(r["times"]))}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -165,6 +165,10 @@ int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold,
 int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n, int group_threshold, double eps,
                                     size_t* count);
 
+/* frames the batch entry point hands to one launch of each kernel for frames of this shape under the handle's current
+ * scale factor / nlevels (instrumentation: bench.py quotes its roofline on launches of this size) */
+int hogb200_batch_group(const hogb200_t* h, int width, int height, int channels);
+
 /* ---- instrumentation for bench.py: device time (ms, CUDA events on the handle's stream) of the stages of
  * the last work call, and the number of kernels it launched. */
 typedef struct hogb200_timings {

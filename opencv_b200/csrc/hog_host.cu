@@ -12,6 +12,7 @@
 #include "hog_internal.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cfloat>
 #include <cstdio>
@@ -436,6 +437,41 @@ int ensure_cand(hogb200* h, size_t cap)
 }
 
 // Queue the three kernels for a group of frames (1 .. P.group) on the handle's stream.
+// Debugging aid (HOGB200_WATCHDOG=<seconds>): an event after every kernel of the batch path; if the stream has not
+// drained after that many seconds, the first unfinished event names the kernel that hangs, and the process aborts.
+struct Watchdog {
+    struct Mark { cudaEvent_t ev; const char* what; int group_frames; };
+    std::vector<Mark> marks; size_t used = 0;
+    double seconds = 0;
+    Watchdog() { const char* e = getenv("HOGB200_WATCHDOG"); seconds = e ? atof(e) : 0; }
+    void mark(cudaStream_t st, const char* what, int nf)
+    {
+        if (seconds <= 0) return;
+        if (used == marks.size()) { Mark m; cudaEventCreateWithFlags(&m.ev, cudaEventDisableTiming); marks.push_back(m); }
+        marks[used].what = what; marks[used].group_frames = nf;
+        cudaEventRecord(marks[used].ev, st);
+        used++;
+    }
+    void drain(cudaStream_t st)
+    {
+        if (seconds <= 0) return;
+        const auto t0 = std::chrono::steady_clock::now();
+        while (cudaStreamQuery(st) == cudaErrorNotReady) {
+            if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > seconds) {
+                for (size_t i = 0; i < used; i++)
+                    if (cudaEventQuery(marks[i].ev) == cudaErrorNotReady) {
+                        fprintf(stderr, "hogb200 watchdog: kernel %zu of %zu since the last drain (%s, %d frames) has not finished after %.0f s\n",
+                                i, used, marks[i].what, marks[i].group_frames, seconds);
+                        break;
+                    }
+                abort();
+            }
+        }
+        used = 0;
+    }
+};
+Watchdog g_watchdog;
+
 int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, const int* slots, float thresh,
                 float* d_scores, int tag, int* launches)
 {
@@ -447,12 +483,14 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
     if (P.n_resize) {
         launch_resize(fs, P.W, P.H, P.cn, P.d_levels.p, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
         (*launches)++;
+        g_watchdog.mark(st, "resize", nframes);
     }
     if (h->timing) cudaEventRecord(h->ev[2], st);
     if (P.n_hist) {
         launch_hist(fs, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
                     make_weights(h->win_sigma), (float)h->l2hys, h->d_hist.p, st);
         (*launches)++;
+        g_watchdog.mark(st, "hist", nframes);
     }
     if (h->timing) cudaEventRecord(h->ev[3], st);
     if (ndet > 0 && P.n_svm) {
@@ -467,6 +505,7 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
         sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
         launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, h->num_sms, st);
         (*launches)++;
+        g_watchdog.mark(st, "svm", nframes);
     }
     if (h->timing) cudaEventRecord(h->ev[4], st);
     CK(cudaGetLastError());
@@ -481,6 +520,7 @@ int fetch_candidates(hogb200* h, std::vector<Candidate>& out, size_t* count)
     const size_t first = std::min<size_t>(h->cand_cap, 4096);
     CK(h->h_cand.reserve(16 + h->cand_cap * sizeof(Candidate)));
     CK(cudaMemcpyAsync(h->h_cand.p, h->d_cand.p, 16 + first * sizeof(Candidate), cudaMemcpyDeviceToHost, st));
+    g_watchdog.drain(st);
     CK(cudaStreamSynchronize(st));
     const size_t n = *reinterpret_cast<unsigned int*>(h->h_cand.p);
     *count = n;
@@ -841,15 +881,25 @@ bool batch_lead_in()
     return v;
 }
 
-// frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup)
-int batch_group()
+// Frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup).  Measured on B200 (bench.py
+// --workload ..., profiles/): 4 suits 1080p and KITTI-sized frames; frames whose whole pyramid is a few megapixels
+// (VGA) need more per launch to fill the persistent kernels' queues; at 4K two base frames (66 MB) still sit in L2
+// for the resize kernel, four do not.
+int batch_group(const hogb200* h, int W, int H, int cn)
 {
-    static const int v = [] {
+    static const int forced = [] {
         const char* e = getenv("HOGB200_GROUP");
         const int n = e ? atoi(e) : 0;
-        return n >= 1 && n <= kMaxGroup ? n : 4;
+        return n >= 1 && n <= kMaxGroup ? n : 0;
     }();
-    return v;
+    if (forced) return forced;
+    std::vector<double> scales;
+    enumerate_levels(W, H, h->g.win_w, h->g.win_h, h->scale0, h->nlevels, scales);
+    double px = 0;
+    for (double s : scales) px += (double)cvRound(W / s) * cvRound(H / s);
+    if ((double)W * H * cn > 16e6) return 2;
+    if (px < 4e6) return px < 1.5e6 ? 16 : 8;
+    return 4;
 }
 
 // One frame through the pipeline; candidates come back sorted by (detector, level, y, x).
@@ -976,7 +1026,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         const hogb200_image* fr = &frames[f0];
         // frames go through the kernels in groups: one launch of each kernel covers `grp` frames, which evens out the
         // tail of the persistent histogram kernel and the last wave of the other two
-        const int grp = std::min(batch_group(), nf);
+        const int grp = std::min(batch_group(h, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels), nf);
         if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, grp))) return rc;
         Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
@@ -1112,6 +1162,12 @@ int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold,
     if (!v.empty()) memcpy(rects, v.data(), v.size() * sizeof(hogb200_rect));
     if (count) *count = v.size();
     return HOGB200_OK;
+}
+
+int hogb200_batch_group(const hogb200_t* h, int width, int height, int channels)
+{
+    if (!h || width <= 0 || height <= 0) return 0;
+    return batch_group(h, width, height, channels == 3 ? 4 : channels);
 }
 
 int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n, int group_threshold, double eps, size_t* count)

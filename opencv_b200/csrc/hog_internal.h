@@ -15,7 +15,10 @@ constexpr int kBins = 9;
 constexpr int kHist = 36;            // floats per block histogram
 constexpr int kMaxLevels = 256;
 constexpr int kMaxDet = 4;
-constexpr int kMaxGroup = 8;         // frames one launch of each kernel can process (frame groups of the batch path)
+#ifndef HOGB200_MAX_GROUP
+#define HOGB200_MAX_GROUP 16
+#endif
+constexpr int kMaxGroup = HOGB200_MAX_GROUP;        // frames one launch of each kernel can process (frame groups of the batch path)
 
 // The frames of one group.  Frame f keeps its pyramid levels at LevelDesc::img + f * pyr_stride and its block
 // histograms at hist + f * hist_stride; level 0 aliases base[f].  Work items carry the frame index.

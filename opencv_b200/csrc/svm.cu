@@ -253,12 +253,17 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
             n += tile_rows;
             const int rest = tile_rows - (band * kBandRows + 7 + win_by);   // rows below the band's last one
             if (wx0 >= vwx || wy0 >= vwy) {                             // nothing to score here
-                for (int r = lane; r < tile_rows; r += 32) {
-                    const unsigned m = tile0 + r;
-                    mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
-                    mbar_arrive(empty0 + 8 * (m % kRing));
+                // Rows 39.. of a tile reuse the slots of its rows 0..: a lane may only test a slot's NEXT use once the
+                // slot's current use is known to have landed (a parity test cannot tell "not yet" from "one phase
+                // ago"), and rows land out of order.  Hence the warp-wide join between the two rounds.
+                for (int r0 = 0; r0 < tile_rows; r0 += 32) {
+                    const unsigned m = tile0 + r0 + lane;
+                    if (r0 + lane < tile_rows) {
+                        mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
+                        mbar_arrive(empty0 + 8 * (m % kRing));
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
                 continue;
             }
             if (lane < band * kBandRows + 7) {                          // the rows above the band + the 7 rows steps 0 and 1 read

@@ -367,6 +367,11 @@ class HOG:
             raise HogError(rc, L.hogb200_last_error().decode())
         return r[:n.value].copy()
 
+    def batchGroup(self, width, height, channels=4):
+        """frames per kernel launch the batch path uses for this frame shape"""
+        self._L.hogb200_batch_group.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        return int(self._L.hogb200_batch_group(self._h, int(width), int(height), int(channels)))
+
     def groupRectanglesDevice(self, rects, group_threshold, eps=0.2):
         """cv::groupRectangles computed on the device (csrc/group.cu): same output as groupRectangles."""
         r = np.ascontiguousarray(np.asarray(rects, np.int32).reshape(-1, 4)).copy()
