@@ -15,7 +15,6 @@ import argparse
 import json
 import os
 import statistics
-import subprocess
 import sys
 import threading
 import time
@@ -73,6 +72,27 @@ def select_workload(name):
                    "l2": "inputs larger than L2 (%d distinct frames = %.0f MB per step per GPU)" % (w["BATCH"], mb)}
 
 
+def bind_near_gpu(local_rank):
+    """Pin this rank's host threads to the CPUs of its GPU's NUMA node BEFORE any pinned buffer is allocated, so
+    that the frames it uploads live in memory local to the GPU's PCIe root (first touch).  With 8 ranks streaming
+    8 MB frames, buffers that all sit on one socket make the upload, not the kernels, the limit.  Best effort."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        txt = open("/sys/bus/pci/devices/%s/local_cpulist" % bdf).read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return "%s numa cpus %s" % (bdf, txt)
+    except Exception as e:      # no sysfs entry, no permission, older torch: stay unbound
+        return "unbound (%s)" % e
+
+
 def make_frames(n, seed0):
     from _oracle import synthetic_frame
     base = [synthetic_frame(seed0 + i, W, H, CN, silhouettes=6) for i in range(min(n, 4))]
@@ -84,45 +104,51 @@ def make_frames(n, seed0):
 
 
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons of this rank's GPU DURING the timed region: NVML polled in-process every 10 ms
+    (nvidia-smi as a subprocess takes longer to start on an 8-GPU box than a timed region lasts)."""
+    REASONS = (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40))
 
     def __init__(self, gpu):
-        self.gpu = gpu; self.rows = []; self.p = None
+        self.gpu = gpu; self.sm = []; self.mx = None; self.reasons = set(); self.stop_flag = False; self.t = None; self.err = None
 
     def start(self):
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
-                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
-        except Exception:
-            self.p = None
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.gpu
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:                                           # NVML numbers the physical devices
+                try:
+                    idx = int(vis.split(",")[self.gpu])
+                except ValueError:
+                    pass
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
 
-    def _read(self):
-        for line in self.p.stdout:
-            self.rows.append(line.strip())
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons") \
+                            else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        for name, bit in self.REASONS:
+                            if r & bit:
+                                self.reasons.add(name)
+                    except Exception as e:
+                        self.err = str(e)
+                    time.sleep(0.01)
+            self.t = threading.Thread(target=loop, daemon=True); self.t.start()
+        except Exception as e:
+            self.err = str(e)
 
     def stop(self):
-        if not self.p:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.p.terminate()
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
-            c = [x.strip() for x in r.split(",")]
-            if len(c) < 8:
-                continue
-            try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self.stop_flag = True
+        if self.t:
+            self.t.join(timeout=1.0)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["NVML unavailable: %s" % self.err], "samples": 0}
+        return {"sm_mhz": statistics.median(self.sm), "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
+                "samples": len(self.sm)}
 
 
 def cpu_reference_fps(frames, nthreads=None):
@@ -201,6 +227,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    binding = bind_near_gpu(local_rank) if world > 1 and os.environ.get("HOGB200_NUMA_BIND", "1") != "0" else "single rank: not bound"
+    print("rank %d: %s" % (rank, binding), file=sys.stderr)
     host_group = None
     if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
         os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
