@@ -513,3 +513,51 @@ def test_dense_hits_grouped_on_device(hog, port):
     ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, -3.0, 2)
     assert ok and len(exp) > 0
     hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+# ------------------------------------------------------------------ detector -> tracker (example_gpu_tbd's loop)
+def _moving_scene(nframes, W=640, H=480):
+    """A fixed textured background with three bright vertical ellipses walking across it."""
+    base = synthetic_frame(4242, W, H, 4).astype(np.float32)
+    yy, xx = np.ogrid[:H, :W]
+    walkers = [(80, 150, 7, 1, 150), (520, 300, -9, -2, 110), (300, 240, 4, 0, 190)]     # x, y, vx, vy, height
+    frames = []
+    for k in range(nframes):
+        img = base.copy()
+        for (x, y, vx, vy, hh) in walkers:
+            cx, cy, ww = x + vx * k, y + vy * k, hh / 3.0
+            m = ((yy - cy) / (hh / 2.0)) ** 2 + ((xx - cx) / (ww / 2.0)) ** 2 <= 1
+            img[m, :3] = img[m, :3] * 0.2 + 200
+        frames.append(np.clip(np.rint(img), 0, 255).astype(np.uint8))
+    return frames
+
+
+def test_detector_feeds_tracker_like_the_sample(hog, port):
+    """samples/gpu/tbd.cpp:596-700 end to end: detectMultiScale (sample settings: nlevels 15, group 2) -> one
+    Detection(-1, frame, rect, -1.0) per grouped rect -> Tracker::performTrackingStep.  This pipeline (GPU detector +
+    tbdb200 tracker) against the oracle detector + the UNMODIFIED reference tracker."""
+    from opencv_b200 import tbd
+    from test_tbd import RefTracker, our_state, same_state
+    det = hog.getDefaultPeopleDetector()
+    args = tbd.TbdArgs(10.0, 16, 4, 0.3, -1.0, 1)
+    ours, ref = tbd.Tracker(args), RefTracker(args)
+    ours.setBounds(0, 640, 0, 480)       # the reference hard-codes 1280x720; these frames are smaller than that
+    hit = -1.6
+    hog.setNumLevels(15); hog.setHitThreshold(hit); hog.setGroupThreshold(2)
+    try:
+        frames = _moving_scene(10)
+        out = hog.detectMultiScaleBatch(frames)
+        seen = 0
+        for k, (img, rects) in enumerate(zip(frames, out)):
+            ok, got, exp = _set_equal_mod_threshold(hog, port, img, det, hit, 2, 1.05, 15)
+            assert ok and np.array_equal(got, rects)                   # batch path == per-frame path == oracle
+            seen += len(rects)
+            d_ours = [tbd.Detection(-1, k, tuple(int(v) for v in r), -1.0) for r in rects]
+            d_ref = [tbd.Detection(-1, k, tuple(int(v) for v in r), -1.0) for r in (exp if len(exp) == len(got) else got)]
+            ours.performTrackingStep(d_ours, k)
+            ref.step(d_ref, k)
+            if np.array_equal(got, exp):
+                assert same_state(our_state(ours), ref.state()), k
+        assert seen > 0
+    finally:
+        hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
