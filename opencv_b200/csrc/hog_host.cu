@@ -472,6 +472,35 @@ struct Watchdog {
 };
 Watchdog g_watchdog;
 
+// Debugging aid (HOGB200_TRACE=1): the upload and kernel intervals of every frame group of a batch call, in ms from
+// the first group's upload, printed to stderr when the call has drained.  Off: no events, no synchronisation.
+struct GroupTrace {
+    struct Row { cudaEvent_t ev[4]; };       // upload begin / end (copy stream), kernels begin / end (compute stream)
+    std::vector<Row> rows; size_t used = 0;
+    const bool on = getenv("HOGB200_TRACE") != nullptr;
+    void begin() { used = 0; }
+    void mark(int which, cudaStream_t st)
+    {
+        if (!on) return;
+        if (which == 0) {
+            if (used == rows.size()) { Row r; for (cudaEvent_t& e : r.ev) cudaEventCreate(&e); rows.push_back(r); }
+            used++;
+        }
+        cudaEventRecord(rows[used - 1].ev[which], st);
+    }
+    void print()
+    {
+        if (!on || !used) return;
+        cudaDeviceSynchronize();
+        for (size_t g = 0; g < used; g++) {
+            float t[4] = {-1, -1, -1, -1};
+            for (int k = 0; k < 4; k++) cudaEventElapsedTime(&t[k], rows[0].ev[0], rows[g].ev[k]);
+            fprintf(stderr, "group %2zu: upload %.3f .. %.3f   kernels %.3f .. %.3f\n", g, t[0], t[1], t[2], t[3]);
+        }
+    }
+};
+GroupTrace g_trace;
+
 int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, const int* slots, float thresh,
                 float* d_scores, int tag, int* launches)
 {
@@ -1030,11 +1059,10 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, grp))) return rc;
         Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
-        static const bool trace = getenv("HOGB200_TRACE") != nullptr;      // debugging aid: per-group timeline on stderr
-        cudaEvent_t tev[kChunk][4]; int ntev = 0;
         for (int attempt = 0; attempt < 2; attempt++) {
             if ((rc = ensure_cand(h, cap))) return rc;
             CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
+            g_trace.begin();
             // Nothing hides the upload of the first group, so when frames come from host memory the batch opens with
             // groups of 1 and grp - 1 frames: the kernels start after one frame's copy instead of a whole group's,
             // and the copies (faster than the kernels per frame) stay ahead from then on.
@@ -1049,8 +1077,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
                 for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
                 if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
                 else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
-                if (trace) { cudaEventCreate(&tev[gi][0]); cudaEventCreate(&tev[gi][1]); cudaEventCreate(&tev[gi][2]); cudaEventCreate(&tev[gi][3]);
-                             cudaEventRecord(tev[gi][0], any_host ? cs : st); }
+                g_trace.mark(0, any_host ? cs : st);
                 for (int j = 0; j < ng; j++) {
                     const hogb200_image* im = fr + g0 + j;
                     // host frames: upload on the copy stream, overlapping the previous group's kernels
@@ -1060,7 +1087,8 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
                     CK(cudaEventRecord(h->up_done[b], cs));
                     CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
                 }
-                if (trace) { cudaEventRecord(tev[gi][1], any_host ? cs : st); cudaEventRecord(tev[gi][2], st); }
+                g_trace.mark(1, any_host ? cs : st);
+                g_trace.mark(2, st);
                 // a group smaller than grp runs on a plan of its own size: work lists dealt for grp frames leave the
                 // persistent kernels unbalanced when most of their items belong to absent frames
                 Plan* Pg = &P;
@@ -1070,21 +1098,11 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
                 }
                 if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches))) return rc;
                 CK(cudaEventRecord(h->fr_done[b], st));
-                if (trace) { cudaEventRecord(tev[gi][3], st); ntev = gi + 1; }
+                g_trace.mark(3, st);
             }
             size_t n = 0;
             rc = fetch_candidates(h, c, &n);
-            if (trace) {
-                cudaDeviceSynchronize();
-                for (int gi = 0; gi < ntev; gi++) {
-                    float a = -1, b2 = -1, c2 = -1, d = -1;
-                    cudaError_t e1 = cudaEventElapsedTime(&a, tev[0][0], tev[gi][0]); cudaEventElapsedTime(&b2, tev[0][0], tev[gi][1]);
-                    cudaEventElapsedTime(&c2, tev[0][0], tev[gi][2]); cudaEventElapsedTime(&d, tev[0][0], tev[gi][3]);
-                    if (e1 != cudaSuccess) fprintf(stderr, "(%s) ", cudaGetErrorString(e1));
-                    fprintf(stderr, "group %2d: upload %.3f .. %.3f   kernels %.3f .. %.3f\n", gi, a, b2, c2, d);
-                }
-                for (int gi = 0; gi < ntev; gi++) for (int k = 0; k < 4; k++) cudaEventDestroy(tev[gi][k]);
-            }
+            g_trace.print();
             if (rc == HOGB200_CAPACITY && attempt == 0) { cap = (size_t)P.nwindows * nslots * nf + 16; continue; }
             if (rc) return rc;
             break;
