@@ -76,8 +76,8 @@ int tbdb200_set_bounds(tbdb200_t* t, int xmin, int xmax, int ymin, int ymax);
 
 /* Tracker::performTrackingStep(detections, trajectoryMap, frame_id)  tbd.cpp:211-298.
  * track_of_detection (optional, n ints): the id of the track each detection was assigned to, -1 if it was left
- * unassigned (and therefore started a new track).  This is what the reference's trajectory bookkeeping
- * (Trajectory::addTrackingInfo, tbd.cpp:151-170) is built from; the ground-truth maps themselves stay with the caller. */
+ * unassigned (and therefore started a new track).  Detections with id >= 0 are also entered into the handle's
+ * trajectory records (below), as the reference enters them into the caller's trajectoryMap. */
 int tbdb200_step(tbdb200_t* t, const tbdb200_detection* detections, int n, int frame_id, int* track_of_detection);
 
 /* Tracker::getTracks()  tbd.cpp:193-196: number of live tracks / their scalar state, in the reference's order. */
@@ -91,6 +91,23 @@ int tbdb200_track_history(const tbdb200_t* t, int index, int* frames, int* boxes
 int tbdb200_copy_tracks(const tbdb200_t* t, tbdb200_trackset_t** out);
 int tbdb200_set_tracks(tbdb200_t* t, const tbdb200_trackset_t* tracks);   /* NULL = no tracks */
 void tbdb200_trackset_destroy(tbdb200_trackset_t* s);
+
+/* ---- ground-truth trajectories (cv::tbd::Trajectory, tbd.hpp:47-73): the sample registers the ground-truth box of
+ * object `id` in frame `frame` (Trajectory::addPosition, tbd.cpp:144-149; samples/gpu/tbd.cpp parseDetections), and a
+ * step records, for every detection with id >= 0, whether it was tracked and by which track
+ * (Trajectory::addTrackingInfo, tbd.cpp:151-175).  The maps live with the handle; tbdb200_reset leaves them alone, as
+ * Tracker::reset leaves the caller's trajectoryMap alone. */
+typedef struct tbdb200_trajectory_frame {
+    int has_info;                 /* 0: this (id, frame) was never reported by a step */
+    int is_tracked;               /* isTrackedPerFrame */
+    int track_id;                 /* trackIdPerFrame            (valid when is_tracked) */
+    int track_pos[4];             /* trackPosPerFrame: the track's newest box, x y width height */
+    int pred_pos[4];              /* predPosPerFrame */
+    double bbox_overlap;          /* bboxOverlapPerFrame: IoU of track_pos with the registered ground-truth box */
+} tbdb200_trajectory_frame;
+int tbdb200_trajectory_add_position(tbdb200_t* t, int id, int frame, const int* box);
+int tbdb200_trajectory_get(const tbdb200_t* t, int id, int frame, tbdb200_trajectory_frame* out);
+int tbdb200_trajectory_clear(tbdb200_t* t);
 
 /* the per-frame metric vectors (one entry per step since the last reset) */
 int tbdb200_metrics(const tbdb200_t* t, tbdb200_frame_metrics* out, int capacity, int* count);

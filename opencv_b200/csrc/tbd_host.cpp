@@ -10,14 +10,18 @@
 //     the same scans are performed here (on a flat matrix with byte masks)                      (tbd.cpp:402-880)
 //   * update: box size stabilised over the last <= 4 boxes in unsigned integer arithmetic, confidence window,
 //     deletion rule, creation from unassigned detections                                        (tbd.cpp:897-1044)
-// What is not carried over: the reference's progress prints to stdout, the random display colour of a track, and the
-// ground-truth Trajectory maps (the step reports the track of every detection instead; see tbdb200.h).
+//   * trajectories: per ground-truth id and frame, whether the detection was tracked, by which track, the track's
+//     newest and predicted boxes and the IoU with the registered ground-truth box                (tbd.cpp:144-175, 236-272)
+// What is not carried over: the reference's progress prints to stdout, the random display colour of a track, and
+// world coordinates (never read by the tracker).
 #include "../../include/tbdb200.h"
 
 #include <emmintrin.h>
 
 #include <algorithm>
+#include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace {
@@ -193,7 +197,11 @@ private:
 
 struct tbdb200_trackset { std::vector<TrackState> tracks; };
 
+struct TrajectoryInfo { bool tracked; unsigned track_id; Box track_pos, pred_pos; double overlap; };
+
 struct tbdb200 {
+    std::map<std::pair<int, int>, Box> gt_position;            // (id, frame) -> Trajectory::positionPerFrame
+    std::map<std::pair<int, int>, TrajectoryInfo> trajectory;  // (id, frame) -> Trajectory::*PerFrame
     tbdb200_args args;
     int xmin = 0, xmax = 1280, ymin = 0, ymax = 720;      // tbd.cpp:222
     unsigned next_id = 0;
@@ -319,6 +327,20 @@ int tbdb200_step(tbdb200_t* t, const tbdb200_detection* det, int n, int frame_id
         tr.overlap = 0.0;
         update_confidence(t, tr);
     }
+    // trajectories of detections that carry a ground-truth id (tbd.cpp:236-272; Trajectory::addTrackingInfo :151-175):
+    // assigned ones in track order, then the unassigned ones; before any track is deleted or created
+    for (unsigned i = 0; i < nt; i++) {
+        if (det_of_track[i] < 0 || det[det_of_track[i]].id < 0) continue;
+        const TrackState& tr = tracks[i];
+        const std::pair<int, int> key(det[det_of_track[i]].id, frame_id);
+        const Box gt = t->gt_position[key];            // a missing position reads as Rect(), as map::operator[] gives it
+        t->trajectory[key] = TrajectoryInfo{true, tr.id, tr.boxes.back(), tr.pred, iou(tr.boxes.back(), gt)};
+    }
+    for (unsigned j : free_dets) {
+        if (det[j].id < 0) continue;
+        TrajectoryInfo& ti = t->trajectory[std::make_pair(det[j].id, frame_id)];
+        ti.tracked = false;                            // the other fields keep what an earlier report left (reference: untouched maps)
+    }
     // deleteLostTracks (tbd.cpp:984-1012)
     tracks.erase(std::remove_if(tracks.begin(), tracks.end(), [&](const TrackState& tr) {
         const double visibility = ((double)tr.visible) / tr.age;
@@ -396,6 +418,35 @@ int tbdb200_set_tracks(tbdb200_t* t, const tbdb200_trackset_t* s)
 }
 
 void tbdb200_trackset_destroy(tbdb200_trackset_t* s) { delete s; }
+
+int tbdb200_trajectory_add_position(tbdb200_t* t, int id, int frame, const int* box)
+{
+    if (!t || !box) return fail("tbdb200_trajectory_add_position: null argument");
+    t->gt_position[std::make_pair(id, frame)] = Box{box[0], box[1], box[2], box[3]};
+    return 0;
+}
+
+int tbdb200_trajectory_get(const tbdb200_t* t, int id, int frame, tbdb200_trajectory_frame* out)
+{
+    if (!t || !out) return fail("tbdb200_trajectory_get: null argument");
+    *out = tbdb200_trajectory_frame();
+    const auto it = t->trajectory.find(std::make_pair(id, frame));
+    if (it == t->trajectory.end()) return 0;
+    const TrajectoryInfo& ti = it->second;
+    out->has_info = 1; out->is_tracked = ti.tracked; out->track_id = (int)ti.track_id;
+    const Box* b[2] = {&ti.track_pos, &ti.pred_pos};
+    int* o[2] = {out->track_pos, out->pred_pos};
+    for (int k = 0; k < 2; k++) { o[k][0] = b[k]->x; o[k][1] = b[k]->y; o[k][2] = b[k]->w; o[k][3] = b[k]->h; }
+    out->bbox_overlap = ti.overlap;
+    return 0;
+}
+
+int tbdb200_trajectory_clear(tbdb200_t* t)
+{
+    if (!t) return fail("tbdb200_trajectory_clear: null handle");
+    t->gt_position.clear(); t->trajectory.clear();
+    return 0;
+}
 
 int tbdb200_metrics(const tbdb200_t* t, tbdb200_frame_metrics* out, int capacity, int* count)
 {

@@ -40,6 +40,12 @@ class Track(C.Structure):
         return (self.x, self.y, self.width, self.height)
 
 
+class TrajectoryFrame(C.Structure):
+    """what cv::tbd::Trajectory holds for one frame (tbd.hpp:60-68)"""
+    _fields_ = [("hasInfo", C.c_int), ("isTracked", C.c_int), ("trackId", C.c_int), ("trackPos", C.c_int * 4),
+                ("predPos", C.c_int * 4), ("bboxOverlap", C.c_double)]
+
+
 class FrameMetrics(C.Structure):
     _fields_ = [("truePositives", C.c_int), ("falseNegatives", C.c_int), ("falsePositives", C.c_int),
                 ("groundTruths", C.c_int), ("numMatches", C.c_int), ("bboxOverlap", C.c_double)]
@@ -65,6 +71,9 @@ def _lib():
         L.tbdb200_set_tracks.argtypes = [C.c_void_p, C.c_void_p]
         L.tbdb200_trackset_destroy.argtypes = [C.c_void_p]; L.tbdb200_trackset_destroy.restype = None
         L.tbdb200_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.tbdb200_trajectory_add_position.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.tbdb200_trajectory_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(TrajectoryFrame)]
+        L.tbdb200_trajectory_clear.argtypes = [C.c_void_p]
         L.tbdb200_bbox_overlap.argtypes = [C.c_void_p, C.c_void_p]; L.tbdb200_bbox_overlap.restype = C.c_double
         _BOUND = True
     return L
@@ -140,6 +149,18 @@ class Tracker:
 
     def setTracks(self, trackset):
         self._ck(self._L.tbdb200_set_tracks(self._h, trackset._h if trackset is not None else None))
+
+    def addPosition(self, id, frame, bbox):
+        """Trajectory::addPosition of ground-truth object `id`"""
+        self._ck(self._L.tbdb200_trajectory_add_position(self._h, int(id), int(frame), (C.c_int * 4)(*map(int, bbox))))
+
+    def trajectoryFrame(self, id, frame):
+        out = TrajectoryFrame()
+        self._ck(self._L.tbdb200_trajectory_get(self._h, int(id), int(frame), C.byref(out)))
+        return out
+
+    def clearTrajectories(self):
+        self._ck(self._L.tbdb200_trajectory_clear(self._h))
 
     def metrics(self):
         cnt = C.c_int()

@@ -99,6 +99,33 @@ void cvref_tbd_restore(void* h, int snapshot)
     r->tracker.setTracks(copy);
 }
 
+// Trajectory::addPosition for ground-truth object `id` (creates the trajectory on first use, like the sample's parser)
+void cvref_tbd_add_position(void* h, int id, int frame, const int* box)
+{
+    RefTracker* r = (RefTracker*)h;
+    if (!r->trajectories.count(id)) r->trajectories[id] = Trajectory(id);
+    Rect bb(box[0], box[1], box[2], box[3]);
+    Vec3d w;
+    r->trajectories[id].addPosition(frame, bb, w);
+}
+// ints: is_tracked, track_id, track_pos[4], pred_pos[4]; returns 0 when the (id, frame) pair was never reported
+int cvref_tbd_trajectory_get(void* h, int id, int frame, int* ints, double* overlap)
+{
+    RefTracker* r = (RefTracker*)h;
+    if (!r->trajectories.count(id)) return 0;
+    Trajectory& t = r->trajectories[id];
+    if (!t.isTrackedPerFrame.count(frame)) return 0;
+    ints[0] = t.isTrackedPerFrame[frame] ? 1 : 0;
+    if (t.trackIdPerFrame.count(frame)) {
+        ints[1] = t.trackIdPerFrame[frame];
+        const Rect a = t.trackPosPerFrame[frame], b = t.predPosPerFrame[frame];
+        ints[2] = a.x; ints[3] = a.y; ints[4] = a.width; ints[5] = a.height;
+        ints[6] = b.x; ints[7] = b.y; ints[8] = b.width; ints[9] = b.height;
+        *overlap = t.bboxOverlapPerFrame[frame];
+    }
+    return 1;
+}
+
 // metrics: count, then per frame ints (tp, fn, fp, gt, matches) and double overlap
 int cvref_tbd_metrics(void* h, int* ints, double* overlap, int cap)
 {

@@ -53,6 +53,15 @@ class RefTracker:
     def reset(self):
         self.L.cvref_tbd_reset(self.h)
 
+    def add_position(self, id, frame, box):
+        self.L.cvref_tbd_add_position(self.h, C.c_int(id), C.c_int(frame), (C.c_int * 4)(*map(int, box)))
+
+    def trajectory(self, id, frame):
+        ints = (C.c_int * 10)(); ov = C.c_double(0.0)
+        if not self.L.cvref_tbd_trajectory_get(self.h, C.c_int(id), C.c_int(frame), ints, C.byref(ov)):
+            return None
+        return list(ints), ov.value
+
     def snapshot(self):
         return self.L.cvref_tbd_snapshot(self.h)
 
@@ -175,6 +184,39 @@ def test_history_age_replay_like_the_sample():
         ref.step(dets, f)
         assert same_state(our_state(ours), ref.state()), k
         ours_buf[k] = ours.copyTracks(); ref_buf[k] = ref.snapshot()
+
+
+@needs_ref
+def test_trajectories_identical_to_reference():
+    """Ground-truth ids on the detections: what Trajectory::addTrackingInfo records per (id, frame) -- tracked or not,
+    by which track, the track's newest and predicted boxes, IoU with the registered ground-truth box."""
+    a = tbd.TbdArgs(10.0, 16, 4, 0.3, -1.0, 1)
+    ours, ref = tbd.Tracker(a), RefTracker(a)
+    rng = np.random.RandomState(31)
+    frames = scene(55, 40, 9, True, clutter=0.5)
+    for f, dets in frames:
+        labelled = []
+        for i, d in enumerate(dets):
+            gid = i if rng.rand() < 0.7 else -1                  # some detections carry no ground truth
+            labelled.append(tbd.Detection(gid, d.frame_id, (d.x, d.y, d.width, d.height), d.confidence))
+            if gid >= 0 and rng.rand() < 0.9:                    # ... and some ids have no registered position
+                gt = (d.x + int(rng.randint(-4, 5)), d.y + int(rng.randint(-4, 5)), d.width, d.height)
+                ours.addPosition(gid, f, gt); ref.add_position(gid, f, gt)
+        ours.performTrackingStep(labelled, f)
+        ref.step(labelled, f)
+        assert same_state(our_state(ours), ref.state()), f
+        for gid in range(-1, len(dets) + 1):
+            want = ref.trajectory(gid, f)
+            got = ours.trajectoryFrame(gid, f)
+            assert bool(got.hasInfo) == (want is not None), (f, gid)
+            if want is None:
+                continue
+            ints, ov = want
+            assert bool(got.isTracked) == bool(ints[0])
+            if ints[0]:
+                assert [got.trackId, *got.trackPos, *got.predPos] == ints[1:] and got.bboxOverlap == ov, (f, gid)
+    ours.clearTrajectories()
+    assert not ours.trajectoryFrame(0, frames[0][0]).hasInfo
 
 
 def test_reports_track_of_each_detection_and_bounds():
