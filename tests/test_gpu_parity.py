@@ -561,3 +561,41 @@ def test_detector_feeds_tracker_like_the_sample(hog, port):
         assert seen > 0
     finally:
         hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_api_edge_cases_of_the_reference(port, tmp_path):
+    """SURVEY.md Appendix C: behaviours of cv::cuda::HOG a drop-in has to keep."""
+    from opencv_b200 import HOG, HogError
+    h = HOG.create()
+    det = h.getDefaultPeopleDetector()
+    h.setSVMDetector(det)
+    assert h.getWinSigma() == 4.0                                   # (block_w + block_h) / 8 while unset (hog.cpp:288-291)
+    assert h.getDescriptorSize() == 3780 and h.getBlockHistogramSize() == 36
+    assert (h.getNumLevels(), h.getHitThreshold(), h.getScaleFactor(), h.getGroupThreshold()) == (64, 0.0, 1.05, 2)
+    # scale0 <= 1: exactly one level (hog.cpp:433) -- detectMultiScale degenerates to detect with 64x128 rects
+    img = synthetic_frame(808, 320, 256, 4, silhouettes=3)
+    h.setScaleFactor(1.0); h.setHitThreshold(-2.0); h.setGroupThreshold(0)
+    assert len(h.levels(320, 256)[0]) == 1
+    r = h.detectMultiScale(img)
+    pts = h.detect(img)
+    assert len(r) == len(pts) > 0 and np.array_equal(r[:, :2], pts) and (r[:, 2:] == (64, 128)).all()
+    er, _ = port.detect_multiscale(img, det, hit_threshold=-2.0, scale0=1.0, group_threshold=0)
+    assert abs(len(r) - len(er)) <= 2
+    # geometries outside block 16x16 / cell 8x8 / 9 bins are refused, not mis-computed (cudaobjdetect.hpp:89-93)
+    for kw in (dict(win_size=(48, 96), block_size=(16, 16), block_stride=(8, 8), cell_size=(4, 4)),
+               dict(win_size=(64, 128), block_size=(32, 32), block_stride=(16, 16), cell_size=(16, 16)),
+               dict(nbins=8)):
+        with pytest.raises(HogError) as e:
+            HOG.create(**kw)
+        assert e.value.status in (1, 4)
+    # load() takes geometry, sigma, threshold, gamma, nlevels and the detector from the file and resets the run-time
+    # parameters to their defaults (hog.cpp:599-630)
+    h.setWinSigma(3.5); h.setNumLevels(17); h.setHitThreshold(1.25); h.setScaleFactor(1.3); h.setGroupThreshold(5)
+    f = str(tmp_path / "det.yml")
+    h.save(f)
+    g = HOG.load(f)
+    assert (g.getWinSigma(), g.getNumLevels()) == (3.5, 17)
+    assert (g.getHitThreshold(), g.getScaleFactor(), g.getGroupThreshold(), g.getWinStride()) == (0.0, 1.05, 2, (8, 8))
+    g.setHitThreshold(-2.0); g.setGroupThreshold(0); g.setWinSigma(-1.0)
+    h.setWinSigma(-1.0)
+    assert np.array_equal(g.detect(img), pts)                       # the detector travelled with the file
