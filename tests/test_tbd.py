@@ -251,3 +251,45 @@ def test_golden_sequence():
         ints = np.array([s[0] for s in st], np.int32).reshape(-1, 13)
         dbl = np.array([s[1] for s in st], np.float64).reshape(-1, 3)
         assert np.array_equal(ints, g["ints_%d" % k]) and np.array_equal(dbl, g["dbl_%d" % k]), k
+
+
+def lattice_scene(seed):
+    """Boxes on a coarse lattice with three widths and two heights: exact ties and equal IoUs everywhere, the inputs
+    on which the assignment procedure's scan order decides the outcome."""
+    rng = np.random.RandomState(seed)
+    a = tbd.TbdArgs(float(rng.choice([0.5, 10.0])), int(rng.randint(1, 8)), int(rng.randint(1, 6)), float(rng.rand()),
+                    float(rng.choice([-1.0, 0.1, 0.5])), 1)
+    n0 = rng.randint(1, 14)
+    frames = []
+    for f in range(12):
+        n = max(0, n0 + rng.randint(-3, 4))
+        frames.append((f, [tbd.Detection(-1, f, (int(rng.randint(0, 12)) * 16, int(rng.randint(0, 8)) * 16,
+                                                   int(rng.choice([32, 48, 64])), int(rng.choice([64, 96]))),
+                                         float(rng.choice([-1.0, 0.3, 0.9]))) for _ in range(n)]))
+    return a, frames
+
+
+@needs_ref
+def test_tie_heavy_lattice_fuzz_identical_to_reference():
+    for seed in range(160):        # (the reference terminates on all of these; see the next test)
+        a, frames = lattice_scene(seed)
+        ours, ref = tbd.Tracker(a), RefTracker(a)
+        for f, dets in frames:
+            ours.performTrackingStep(dets, f)
+            ref.step(dets, f)
+            assert same_state(our_state(ours), ref.state()), (seed, f)
+
+
+def test_terminates_where_the_reference_spins():
+    """On some tie-heavy inputs the reference's assignment loop never exits (seeds 253, 303, 364 of the lattice fuzz:
+    `while (true)` in tbd.cpp:571-877 keeps re-deriving the same partial assignment).  tbdb200 caps the passes and
+    returns the partial assignment the loop is stuck on; nothing to compare against, but it must come back."""
+    import time
+    for seed in (253, 303, 364):
+        a, frames = lattice_scene(seed)
+        t = tbd.Tracker(a)
+        t0 = time.time()
+        for f, dets in frames:
+            got = t.performTrackingStep(dets, f)
+            assert len(got) == len(dets)
+        assert time.time() - t0 < 5.0
