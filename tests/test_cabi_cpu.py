@@ -77,3 +77,18 @@ def test_group_rectangles_equals_oracle():
         assert np.array_equal(a, b), (n, thr)
         if Ref.available() and n:
             assert np.array_equal(a, Ref().group_rectangles(r, thr))
+
+
+@pytest.mark.skipif(not Ref.available(), reason="oracle/_ref/libcvref.so not built")
+def test_group_rectangles_lattice_fuzz_vs_reference():
+    """Tie-heavy inputs (rects on a lattice, a handful of sizes, eps at and around the similarity boundary): classes,
+    their order, the float means and the inside-a-stronger-class filter equal the unmodified cv::groupRectangles."""
+    ref = Ref()
+    for seed in range(200):
+        rng = np.random.RandomState(seed)
+        n = int(rng.randint(1, 120))
+        s = rng.choice([32, 40, 48, 64, 65, 80], n)
+        r = np.stack([rng.randint(0, 20, n) * rng.choice([4, 8]), rng.randint(0, 12, n) * rng.choice([4, 8]), s, 2 * s], 1).astype(np.int32)
+        for thr in (1, 2, 3):
+            for eps in (0.2, 0.5, 0.05):
+                assert np.array_equal(HOG.groupRectangles(r, thr, eps), ref.group_rectangles(r, thr, eps)), (seed, thr, eps)
