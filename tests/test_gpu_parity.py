@@ -599,3 +599,18 @@ def test_api_edge_cases_of_the_reference(port, tmp_path):
     g.setHitThreshold(-2.0); g.setGroupThreshold(0); g.setWinSigma(-1.0)
     h.setWinSigma(-1.0)
     assert np.array_equal(g.detect(img), pts)                       # the detector travelled with the file
+
+
+def test_group_rectangles_device_lattice_fuzz(hog):
+    """Tie-heavy inputs (rects on a lattice, a handful of sizes, eps at and around the similarity boundary) through the
+    device path: equal to the host restatement, which tests/test_cabi_cpu.py pins to the unmodified reference on the
+    same generator."""
+    from opencv_b200 import HOG
+    for seed in range(60):
+        rng = np.random.RandomState(seed)
+        n = int(rng.randint(1, 400))
+        s = rng.choice([32, 40, 48, 64, 65, 80], n)
+        r = np.stack([rng.randint(0, 20, n) * rng.choice([4, 8]), rng.randint(0, 12, n) * rng.choice([4, 8]), s, 2 * s], 1).astype(np.int32)
+        for thr in (1, 2, 3):
+            for eps in (0.2, 0.5, 0.05):
+                assert np.array_equal(hog.groupRectanglesDevice(r, thr, eps), HOG.groupRectangles(r, thr, eps)), (seed, thr, eps)
