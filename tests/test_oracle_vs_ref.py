@@ -183,3 +183,18 @@ def test_detect_multiscale_vs_reference_pieces(libs):
     assert np.array_equal(got, exp)
     raw, conf = port.detect_multiscale(img, det, hit_threshold=hit, group_threshold=0)
     assert np.array_equal(raw, cand) and np.all(conf >= hit)
+
+
+def test_random_shapes_fuzz():
+    """Random sizes (odd widths, scalar-tail columns, exact halves, up- and down-scaling), blurred or raw noise, both
+    channel counts: pyramid levels and window descriptors of the restatement are BIT-equal to the unmodified reference."""
+    ref, port = Ref(), Port()
+    for seed in range(24):
+        rng = np.random.RandomState(seed)
+        W = int(rng.randint(64, 420)); H = int(rng.randint(128, 360)); cn = int(rng.choice([1, 4]))
+        img = synthetic_frame(seed, W, H, cn, blur=bool(rng.rand() < 0.7), silhouettes=int(rng.randint(0, 3)))
+        half = rng.rand() < 0.2
+        dw = W // 2 if half else int(rng.randint(64, W + 40)); dh = H // 2 if half else int(rng.randint(64, H + 40))
+        assert np.array_equal(port.resize(img, dw, dh), ref.resize(img, dw, dh)), (seed, W, H, cn, dw, dh)
+        bgr = np.ascontiguousarray(img[:, :, :3]) if cn == 4 else img
+        assert np.array_equal(port.compute(img, win_stride=(8, 8)), ref.compute(bgr, win_stride=(8, 8))), (seed, W, H, cn)
