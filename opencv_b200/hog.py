@@ -99,6 +99,7 @@ def load_library():
                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.hogb200_group_rectangles.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
     L.hogb200_group_rectangles_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
+    L.hogb200_batch_group.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     L.hogb200_model_read.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_model_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t]
     L.hogb200_save.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]
@@ -374,7 +375,6 @@ class HOG:
 
     def batchGroup(self, width, height, channels=4):
         """frames per kernel launch the batch path uses for this frame shape"""
-        self._L.hogb200_batch_group.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
         return int(self._L.hogb200_batch_group(self._h, int(width), int(height), int(channels)))
 
     def groupRectanglesDevice(self, rects, group_threshold, eps=0.2):
