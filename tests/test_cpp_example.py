@@ -34,4 +34,5 @@ def test_cpp_example_tracks_the_walkers():
     lines = p.stdout.splitlines()
     assert sum(l.startswith("frame") for l in lines) == 12
     tracks = [l for l in lines if l.startswith("track")]
-    assert len(tracks) >= 1 and any("age 1" not in l for l in tracks), p.stdout
+    ages = [int(l.split("age ")[1].split(",")[0]) for l in tracks]
+    assert len(tracks) >= 1 and max(ages) >= 6, p.stdout            # a walker is followed through most of the 12 frames
