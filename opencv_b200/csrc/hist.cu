@@ -74,10 +74,6 @@ __device__ __forceinline__ float2 lds64(unsigned a)
     asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
     return v;
 }
-__device__ __forceinline__ void sts64(unsigned a, float2 v)
-{
-    asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a), "f"(v.x), "f"(v.y));
-}
 // one vote = two adjacent accumulator rows (bin0 and bin0 + 1), 512 B apart
 // OFF = byte offset of the slot: the three slots sit at fixed immediates from one address register
 template <int OFF>
@@ -97,12 +93,6 @@ __device__ __forceinline__ void sts32x2(unsigned a, float2 v)
 __device__ __forceinline__ void sts64_zero(unsigned a)
 {
     asm volatile("st.shared.v2.f32 [%0], {%1,%1};" ::"r"(a), "f"(0.f));
-}
-__device__ __forceinline__ float4 lds128(unsigned a)
-{
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
-    return v;
 }
 __device__ __forceinline__ void sts128_zero(unsigned a)
 {
