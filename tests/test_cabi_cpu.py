@@ -92,3 +92,11 @@ def test_group_rectangles_lattice_fuzz_vs_reference():
         for thr in (1, 2, 3):
             for eps in (0.2, 0.5, 0.05):
                 assert np.array_equal(HOG.groupRectangles(r, thr, eps), ref.group_rectangles(r, thr, eps)), (seed, thr, eps)
+
+
+def test_headers_are_plain_c(tmp_path):
+    """The boundary is a C ABI: both headers must compile as C99 (no C++ types, no torch types in the signatures)."""
+    import subprocess
+    src = tmp_path / "abi.c"
+    src.write_text('#include "hogb200.h"\n#include "tbdb200.h"\nint main(void) { hogb200_geom g; tbdb200_args a; (void)g; (void)a; return 0; }\n')
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), str(src)])
