@@ -1,17 +1,22 @@
 #!/usr/bin/env python
 """bench.py -- HOG detectMultiScale frames/s at 1080p (BASELINE.json metric), one process per GPU.
 
-A step = one pass of the hot path (pyramid -> fused gradient+histogram -> SVM+compaction -> host grouping) over one
+A step = one pass of the hot path (pyramid -> fused gradient+histogram -> SVM+compaction -> rects + grouping) over one
 batch of BATCH synthetic 1920x1080 8UC4 frames (BASELINE configs[1]: people detector, nlevels=64, scale 1.05).
 
-  value     frames/s, whole job, frames already resident in HBM when the timed region starts
-  e2e       same metric through the public call with PINNED HOST frames (H2D + result D2H inside the timed region)
-  roofline  fused gradient+histogram kernel: algorithmic bytes ((cn + 2.25) B per pyramid pixel) / its CUDA-event time
-  cpu_baseline  the reference's cv::HOGDescriptor::detectMultiScale (oracle/_ref) on the host cores, bounded sample
+  value          frames/s, whole job, frames already resident in HBM when the timed region starts
+  e2e            same metric through the public call with PINNED HOST frames (H2D + result D2H inside the timed region)
+  e2e_with_hits  the e2e measurement again at a hit threshold that makes every frame yield thousands of candidates and
+                 grouped rects, so that compaction, the candidate D2H, rect scaling and groupRectangles are timed too
+  sustained      `value` measured over seconds instead of 20 steps (clocks settle under load)
+  roofline       fused gradient+histogram kernel: algorithmic bytes ((cn + 2.25) B per pyramid pixel) / its CUDA-event
+                 time against the measured HBM peak, and its warp-instruction count against the issue peak
+  cpu_baseline   the reference's cv::HOGDescriptor::detectMultiScale (oracle/_ref) on the host cores, bounded sample
 
 `--impl reference` times only the reference CPU implementation (rank 0), same metric and config.
 """
 import argparse
+import hashlib
 import json
 import os
 import statistics
@@ -29,13 +34,12 @@ W, H, CN = 1920, 1080, 4
 NLEVELS, SCALE0, HIT, GROUP = 64, 1.05, 0.0, 2
 NSLOTS = 1
 BATCH = 32                       # frames per step per GPU: 32 x 8.3 MB = 265 MB of distinct input > 126 MB L2
+WIN = (64, 128)
 METRIC = "HOG detectMultiScale frames/s at 1080p"
 UNIT = "frames/s"
-CONFIG = {"workload": "cv::cuda::HOG people detector, synthetic 1920x1080 8UC4, nlevels=64, scale 1.05, "
-                      "hit_threshold 0, group_threshold 2 (BASELINE configs[1])",
-          "frames_per_step_per_gpu": BATCH, "levels": 44, "pyramid_pixels": 21995553, "windows": 261558,
-          "parallelism": "frame-sharded (frame g -> rank g % N), no collective on the data path, host gather of boxes",
-          "l2": "inputs larger than L2 (32 distinct frames = 265 MB per step per GPU)"}
+WORKLOAD = ("cv::cuda::HOG people detector, synthetic 1920x1080 8UC4, nlevels=64, scale 1.05, "
+            "hit_threshold 0, group_threshold 2 (BASELINE configs[1])")
+PARALLELISM = "frame-sharded (frame g -> rank g % N), no collective on the data path, host gather of boxes"
 
 # The driver's line is the default workload (BASELINE.json's metric is quoted on configs[1]).  north_star also asks for
 # frames/s "on synthetic frames of each named shape": --workload selects the other BASELINE configs; the line keeps the
@@ -66,10 +70,27 @@ def select_workload(name):
     for k in ("W", "H", "CN", "NLEVELS", "SCALE0", "HIT", "GROUP", "NSLOTS", "BATCH"):
         g[k] = w[k]
     g["METRIC"] = w["metric"]
-    mb = w["BATCH"] * w["W"] * w["H"] * w["CN"] / 1e6
-    g["CONFIG"] = {"workload": w["name"], "frames_per_step_per_gpu": w["BATCH"],
-                   "parallelism": CONFIG["parallelism"],
-                   "l2": "inputs larger than L2 (%d distinct frames = %.0f MB per step per GPU)" % (w["BATCH"], mb)}
+    g["WORKLOAD"] = w["name"]
+
+
+def make_config():
+    """The same dict from both arms (the driver compares them): the workload and its work sizes, computed from the level
+    rule on the host (hogb200_enumerate_levels needs no GPU)."""
+    from opencv_b200 import HOG
+    sc, lw, lh = HOG.enumerateLevels(W, H, WIN, SCALE0, NLEVELS)
+    px = int(sum(int(a) * int(b) for a, b in zip(lw, lh)))
+    wins = int(sum(((int(a) - WIN[0]) // 8 + 1) * ((int(b) - WIN[1]) // 8 + 1) for a, b in zip(lw, lh)
+                   if a >= WIN[0] and b >= WIN[1]))
+    mb = BATCH * W * H * CN / 1e6
+    return {"workload": WORKLOAD, "frames_per_step_per_gpu": BATCH, "levels": len(sc), "pyramid_pixels": px,
+            "windows": wins, "detectors": NSLOTS, "parallelism": PARALLELISM,
+            "l2": "inputs larger than L2 (%d distinct frames = %.0f MB per step per GPU)" % (BATCH, mb)}
+
+
+def git_blob_hash(path):
+    """`git hash-object` of a file (the ncu capture is stamped with the hash of the kernel source it was taken from)."""
+    data = open(path, "rb").read()
+    return hashlib.sha1(b"blob %d\0" % len(data) + data).hexdigest()
 
 
 def bind_near_gpu(local_rank):
@@ -95,7 +116,7 @@ def bind_near_gpu(local_rank):
 
 def make_frames(n, seed0):
     from _oracle import synthetic_frame
-    base = [synthetic_frame(seed0 + i, W, H, CN, silhouettes=6) for i in range(min(n, 4))]
+    base = [synthetic_frame(seed0 + i, W, H, CN, silhouettes=6) for i in range(min(n, 8))]
     frames = []
     for i in range(n):                     # distinct bytes per frame without paying n full syntheses
         f = np.roll(base[i % len(base)], shift=(7 * (i // len(base)), 13 * (i // len(base))), axis=(0, 1)).copy()
@@ -108,8 +129,9 @@ class ClockSampler:
     (nvidia-smi as a subprocess takes longer to start on an 8-GPU box than a timed region lasts)."""
     REASONS = (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40))
 
-    def __init__(self, gpu):
+    def __init__(self, gpu, period=0.01):
         self.gpu = gpu; self.sm = []; self.mx = None; self.reasons = set(); self.stop_flag = False; self.t = None; self.err = None
+        self.period = period
 
     def start(self):
         try:
@@ -136,10 +158,11 @@ class ClockSampler:
                                 self.reasons.add(name)
                     except Exception as e:
                         self.err = str(e)
-                    time.sleep(0.01)
+                    time.sleep(self.period)
             self.t = threading.Thread(target=loop, daemon=True); self.t.start()
         except Exception as e:
             self.err = str(e)
+        return self
 
     def stop(self):
         self.stop_flag = True
@@ -151,14 +174,37 @@ class ClockSampler:
                 "samples": len(self.sm)}
 
 
+def host_cores():
+    """Threads the CPU arm may use: every core this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its
+    workers; that is a default for torch's own pools, not a property of the box, and is deliberately overridden."""
+    return max(1, len(os.sched_getaffinity(0)))
+
+
+def unleash_openmp(n):
+    """Make the reference's `#pragma omp parallel for num_threads(n)` (core/src/parallel.cpp:523) really get n threads:
+    the reference switches OpenMP's dynamic adjustment on at load time (parallel.cpp:403-411), and libgomp then caps every
+    team at the OMP_NUM_THREADS it saw at start-up -- 1 under torchrun.  So: the environment before libgomp loads, and
+    dynamic adjustment off + the thread count on the runtime libcvref.so is linked against."""
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    os.environ["OMP_DYNAMIC"] = "FALSE"
+    try:
+        import ctypes
+        g = ctypes.CDLL("libgomp.so.1", mode=ctypes.RTLD_GLOBAL)
+        g.omp_set_dynamic(0)
+        g.omp_set_num_threads(int(n))
+    except OSError:
+        pass
+
+
 def cpu_reference_fps(frames, nthreads=None):
     """The reference's own CPU path on this box's host cores (oracle/_ref), else the C port.  Test/bench
     infrastructure only -- never on the product path."""
     from _oracle import Ref, Port
     if Ref.available():
+        unleash_openmp(nthreads or host_cores())
         ref = Ref()
-        if nthreads:
-            ref.set_num_threads(nthreads)
+        ref.set_num_threads(nthreads or host_cores())
+        unleash_openmp(nthreads or host_cores())      # again: loading the library switched dynamic adjustment back on
         det = ref.people_detector(0)
         cores = ref.get_num_threads()
         t = []
@@ -193,12 +239,13 @@ def run_reference(args, rank):
     fps = args.steps / total
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(CONFIG, frames_per_step_per_gpu=1,
-                           note="stock cv::HOGDescriptor::detectMultiScale (CPU, BGR view of the same BGRA frames), "
-                                "1 frame per step"),
-            "cpu_baseline": {"value": fps, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                             "sample": "%d x 1 frame %dx%d, %s threads (OpenMP parallel_for_ over levels)" % (args.steps, W, H, r["cores"])},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": make_config(),
+            "sample_frames_per_step": 1,
+            "note": "stock cv::HOGDescriptor::detectMultiScale (CPU, BGR view of the same BGRA frames); each step is a bounded "
+                    "sample of the workload: 1 frame",
+            "cpu_baseline": {"value": fps, "unit": UNIT, "cores": r["cores"], "host_cores": host_cores(), "kind": r["kind"],
+                             "sample": "%d x 1 frame %dx%d, %s threads of %d host cores (OpenMP parallel_for_ over levels)"
+                                       % (args.steps, W, H, r["cores"], host_cores())},
             "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -210,6 +257,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--quick", action="store_true", help="skip the with-hits, pass-all and sustained legs (profiling runs)")
+    ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained-clock leg (0 = skip)")
     ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS), help="BASELINE config (default: the metric's)")
     args = ap.parse_args()
     select_workload(args.workload)
@@ -223,6 +272,7 @@ def main():
     import torch
     import torch.distributed as dist
     from opencv_b200 import HOG
+    from opencv_b200.shard import shard_indices, gather_detections
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
@@ -236,10 +286,12 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         host_group = dist.new_group(backend="gloo")        # the host gather of boxes (no collective on the data path)
 
+    CONFIG = make_config()
     hog = HOG.create(device=local_rank)
-    hog.setSVMDetector(hog.getDefaultPeopleDetector())
+    people = hog.getDefaultPeopleDetector()
+    hog.setSVMDetector(people)
     if NSLOTS > 1:       # the reference ships no vehicle model: fixed-seed stand-in, same geometry
-        veh = hog.getDefaultPeopleDetector() + 0.02 * np.random.RandomState(3).standard_normal(3781).astype(np.float32)
+        veh = people + 0.02 * np.random.RandomState(3).standard_normal(3781).astype(np.float32)
         hog.setSVMDetector(veh.astype(np.float32), 1)
     hog.setNumLevels(NLEVELS); hog.setScaleFactor(SCALE0); hog.setHitThreshold(HIT); hog.setGroupThreshold(GROUP)
     stream = torch.cuda.Stream()
@@ -258,49 +310,106 @@ def main():
         torch.cuda.synchronize()
 
     # global frame g of a step lives on rank g % world (opencv_b200/shard.py); this rank holds its BATCH frames
-    my_ids = list(range(rank, BATCH * world, world))
+    n_global = BATCH * world
+    my_ids = shard_indices(n_global, rank, world)
 
-    def timed(frames, steps, gather=False):
+    def one_step(frames, gather, capacity):
+        out = hog.detectMultiScaleBatch(frames, nslots=NSLOTS, capacity=capacity)
+        if NSLOTS > 1:                             # one list per frame: its detectors' boxes together
+            out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(frames))]
+        t = hog.lastTimings()
+        if gather:                                 # boxes of all ranks -> rank 0, frame order, on the host (shard.py)
+            merged = gather_detections(dict(zip(my_ids, out)), n_global, rank, world, group=host_group)
+            assert merged is None or len(merged) == n_global
+        return sum(len(o) for o in out), t["kernel_launches"], t["candidates"]
+
+    def timed(frames, steps, gather=False, capacity=1 << 20, seconds=None):
+        """K steps (or, with `seconds`, as many steps as fit) between two events on the launching stream."""
         barrier()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        nrects = 0; launches = 0; cands = 0
+        nrects = 0; launches = 0; cands = 0; done = 0
+        t0 = time.perf_counter()
         with torch.cuda.stream(stream):
             e0.record(stream)
-            for _ in range(steps):
-                out = hog.detectMultiScaleBatch(frames, nslots=NSLOTS, capacity=1 << 20)
-                if NSLOTS > 1:                             # one list per frame: its detectors' boxes together
-                    out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(frames))]
-                nrects += sum(len(o) for o in out)
-                t = hog.lastTimings(); launches += t["kernel_launches"]; cands += t["candidates"]
-                if gather and world > 1:                   # boxes of all ranks -> rank 0, frame order, on the host
-                    parts = [None] * world if rank == 0 else None
-                    dist.gather_object(dict(zip(my_ids, out)), parts, dst=0, group=host_group)
-                    if rank == 0:
-                        merged = {}
-                        for q in parts:
-                            merged.update(q)
-                        assert len(merged) == BATCH * world
+            while done < steps or (seconds is not None and time.perf_counter() - t0 < seconds):
+                a, b, c = one_step(frames, gather, capacity)
+                nrects += a; launches += b; cands += c; done += 1
             e1.record(stream)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         if world > 1:
             tms = torch.tensor([ms], device="cuda"); dist.all_reduce(tms, op=dist.ReduceOp.MAX); ms = float(tms.item())
         barrier()
-        return ms, nrects, launches, cands
+        return ms, nrects, launches, cands, done
 
     # ---- device-resident inputs (value)
     timed(dev, args.warmup)
-    sampler = ClockSampler(local_rank); sampler.start()
-    ms, nrects, launches, _ = timed(dev, args.steps)
+    sampler = ClockSampler(local_rank).start()
+    ms, nrects, launches, _, _ = timed(dev, args.steps)
     clocks = sampler.stop()
     fps = world * BATCH * args.steps / (ms * 1e-3)
 
     # ---- end to end: pinned host frames through the same public call
     timed(pinned_np, args.warmup, gather=True)
-    ms_e2e, nrects_e2e, _, cands_e2e = timed(pinned_np, args.steps, gather=True)
+    ms_e2e, nrects_e2e, _, cands_e2e, _ = timed(pinned_np, args.steps, gather=True)
     fps_e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
     h2d = BATCH * W * H * CN
     d2h = int(16 * ((BATCH + 63) // 64) + 16 * max(cands_e2e, 0) / max(args.steps, 1))
+
+    line = {"metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": CONFIG, "clocks": clocks,
+            "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "detections_per_step": nrects / max(args.steps, 1)}
+
+    # ---- the same end-to-end measurement with detections: a hit threshold at which every frame yields thousands of
+    # candidates (chosen from frame 0's own score distribution), so compaction under load, the candidate D2H, the
+    # ordering, rect scaling and groupRectangles (hog.cpp:471-487) are inside a timed number
+    if not args.quick:
+        hog.setHitThreshold(-100.0); hog.setGroupThreshold(0)
+        _, sc0 = hog.detectMultiScale(dev[0], confidences=True)
+        target = min(4000, max(1, len(sc0) // 8))
+        thr = float(np.sort(sc0)[-target]) if len(sc0) else 0.0
+        hog.setHitThreshold(thr); hog.setGroupThreshold(max(GROUP, 2))
+        timed(pinned_np, 3, gather=True)
+        ms_h, nrects_h, _, cands_h, _ = timed(pinned_np, args.steps, gather=True)
+        timed(dev, 3)
+        ms_hr, _, _, _, _ = timed(dev, args.steps)
+        line["e2e_with_hits"] = {"value": world * BATCH * args.steps / (ms_h * 1e-3), "unit": UNIT,
+                                 "resident_value": world * BATCH * args.steps / (ms_hr * 1e-3),
+                                 "hit_threshold": thr, "group_threshold": max(GROUP, 2),
+                                 "candidates_per_step": cands_h / args.steps, "candidates_per_frame": cands_h / args.steps / BATCH,
+                                 "detections_per_step": nrects_h / args.steps,
+                                 "h2d_bytes_per_step": h2d,
+                                 "d2h_bytes_per_step": int(16 * ((BATCH + 63) // 64) + 16 * cands_h / args.steps),
+                                 "ms_per_step": ms_h / args.steps}
+        hog.setHitThreshold(HIT); hog.setGroupThreshold(GROUP)
+
+    # ---- dense-pyramid stress, "max candidate windows" for real (SURVEY.md 8(d) config 5): the stock bias gives ~0
+    # hits on synthetic frames, so the run is repeated with a bias that makes every window pass
+    if args.workload == "dense" and not args.quick:
+        allpass = people.copy(); allpass[-1] = 100.0
+        hog.setSVMDetector(allpass)
+        nb = min(8, BATCH)
+        cap = nb * CONFIG["windows"] + 1024
+        timed(dev[:nb], 2, capacity=cap)
+        ms_p, nrects_p, _, cands_p, _ = timed(dev[:nb], 5, capacity=cap)
+        timed(pinned_np[:nb], 1, gather=True, capacity=cap)
+        ms_pe, _, _, _, _ = timed(pinned_np[:nb], 5, gather=True, capacity=cap)
+        line["pass_all_bias"] = {"value": world * nb * 5 / (ms_p * 1e-3), "e2e_value": world * nb * 5 / (ms_pe * 1e-3), "unit": UNIT,
+                                 "frames_per_step_per_gpu": nb, "candidates_per_frame": cands_p / 5 / nb,
+                                 "rects_per_frame": nrects_p / 5 / nb,
+                                 "d2h_bytes_per_step": int(16 * cands_p / 5), "ms_per_step": ms_p / 5,
+                                 "note": "default weights, bias +100: every window of every level is a candidate"}
+        hog.setSVMDetector(people)
+
+    # ---- seconds-long run at settled clocks
+    if args.sustain > 0 and not args.quick:
+        s2 = ClockSampler(local_rank, 0.05).start()
+        ms_s, _, _, _, n_s = timed(dev, 1, seconds=args.sustain)
+        line["sustained"] = {"value": world * BATCH * n_s / (ms_s * 1e-3), "unit": UNIT, "seconds": ms_s * 1e-3, "steps": n_s,
+                             "clocks": s2.stop()}
 
     # ---- per-kernel device times (CUDA events on the launching stream, inside the library) for the roofline.
     # The timed region above issues one launch of each kernel per GROUP of frames (4 by default), so the roofline
@@ -319,6 +428,7 @@ def main():
                 ks[k].append(t[k]); ks1[k].append(t1[k])
     hog.enableTiming(False)
     tinfo = hog.lastTimings()
+    assert int(tinfo["pyramid_pixels"]) == CONFIG["pyramid_pixels"] and int(tinfo["windows"]) == CONFIG["windows"]
     hist_ms = statistics.mean(ks["hist_ms"])
     alg_bytes = (CN + 2.25) * tinfo["pyramid_pixels"] * group
     peaks = {}
@@ -327,41 +437,44 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic = None
+    # the committed `ncu --set full` capture of this kernel: quoted only if it was taken from the hist.cu that is running
+    traffic, util, issue, cap_note = None, {}, None, "no capture"
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json"))).get("dram_bytes_per_launch")
-    except Exception:
-        pass
+        cap = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json")))
+        now = git_blob_hash(os.path.join(ROOT, "opencv_b200", "csrc", "hist.cu"))
+        if args.workload != "1080p":
+            cap_note = "the committed ncu capture is of the 1080p launch"
+        elif cap.get("source_hash", {}).get("opencv_b200/csrc/hist.cu") != now:
+            cap_note = "stale: profiles/hist_kernel_traffic.json was captured from another hist.cu (%s)" % str(cap.get("source_hash"))
+        else:
+            traffic, util, cap_note = cap.get("dram_bytes_per_launch"), cap.get("ncu", {}), "ncu capture of this hist.cu (%s)" % now[:12]
+            sm_hz = 1e6 * float(clocks["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0))
+            nsm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+            slots = nsm * 4 * sm_hz * hist_ms * 1e-3          # warp-instruction issue slots of the launch: SMs x 4 schedulers x clocks
+            issue = {"warp_inst_per_launch": util.get("warp_instructions"), "peak_warp_inst_per_launch": slots,
+                     "frac": util.get("warp_instructions", 0) / slots if slots else None,
+                     "thread_inst_per_pixel": 32 * util.get("warp_instructions", 0) / (tinfo["pyramid_pixels"] * group),
+                     "fp32_pipe_pct_ncu": util.get("fma_pipe_pct"), "issue_active_pct_ncu": util.get("issue_active_pct"),
+                     "how": "smsp__inst_executed.sum of the capture / (SMs x 4 x median SM clock of this run x live launch time)"}
+    except Exception as e:
+        cap_note = "no capture (%s)" % e
     achieved = alg_bytes / (hist_ms * 1e-3) / 1e9
-    util = {}
-    try:
-        util = json.load(open(os.path.join(ROOT, "profiles", "hist_kernel_traffic.json"))).get("ncu", {})
-    except Exception:
-        pass
-    CONFIG.update(levels=len(hog.levels(W, H)[0]), pyramid_pixels=int(tinfo["pyramid_pixels"]), windows=int(tinfo["windows"]))
-    if args.workload != "1080p":
-        traffic, util = None, {}          # the committed ncu capture is of the 1080p launch
-    roofline = {"kernel": "hist_kernel<%d> (fused gradient + histogram + L2-Hys, all %d levels of %d frames in one launch)" % (CN, CONFIG["levels"], group),
-                "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "limiter": "instruction issue + shared-memory bandwidth (DESIGN.md 4.1), not HBM",
-                "ncu": util, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": hist_ms,
-                "frames_per_launch": group,
-                "stage_ms_per_launch": {k: statistics.mean(v) for k, v in ks.items()},
-                "stage_ms_single_frame_launch": {k: statistics.mean(v) for k, v in ks1.items()}}
-
-    line = {"metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": CONFIG, "clocks": clocks,
-            "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches, "detections_per_step": nrects / max(args.steps, 1), "roofline": roofline}
+    line["roofline"] = {
+        "kernel": "hist_kernel<%d> (fused gradient + histogram + L2-Hys, all %d levels of %d frames in one launch)" % (CN, CONFIG["levels"], group),
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": traffic, "issue": issue, "capture": cap_note,
+        "limiter": "instruction issue + shared-memory bandwidth (DESIGN.md 4.1): HBM would bound it only below ~35 instructions/pixel",
+        "ncu": util, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+        "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": hist_ms, "frames_per_launch": group,
+        "stage_ms_per_launch": {k: statistics.mean(v) for k, v in ks.items()},
+        "stage_ms_single_frame_launch": {k: statistics.mean(v) for k, v in ks1.items()}}
 
     if rank == 0 and world == 1 and not args.no_cpu:
         r = cpu_reference_fps([host[0]])                      # warm-up
         r = cpu_reference_fps([host[i % BATCH] for i in range(8 if W * H < 4000000 else 4)])
         total = sum(r["times"])
-        line["cpu_baseline"] = {"value": len(r["times"]) / total, "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+        line["cpu_baseline"] = {"value": len(r["times"]) / total, "unit": UNIT, "cores": r["cores"], "host_cores": host_cores(),
+                                "kind": r["kind"],
                                 "sample": "%d frames %dx%d of the same workload, stock cv::HOGDescriptor::detectMultiScale%s, "
                                           "best frame %.1f ms" % (len(r["times"]), W, H, " (once per detector)" if NSLOTS > 1 else "",
                                                                   1e3 * min(r["times"]))}

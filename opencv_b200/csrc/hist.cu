@@ -553,12 +553,16 @@ void launch_hist(const FrameSet& fs, const LevelDesc* d_levels, const HistItem* 
 {
     if (nitems <= 0) return;
     const int grid = max(1, min(num_sms, (nitems + kWarps - 1) / kWarps));
-    // per-device attribute (cheap host call); the handle may live on any device
+    // the opt-in shared-memory size is a per-device function attribute: set once per device, not per launch
+    static bool attr_set[2][64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bool& done = attr_set[cn == 4][dev & 63];
     if (cn == 4) {
-        cudaFuncSetAttribute(hist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        if (!done) done = cudaFuncSetAttribute(hist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)) == cudaSuccess;
         hist_kernel<4><<<grid, kThreads, sizeof(Smem), st>>>(fs, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
     } else {
-        cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        if (!done) done = cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)) == cudaSuccess;
         hist_kernel<1><<<grid, kThreads, sizeof(Smem), st>>>(fs, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
     }
 }

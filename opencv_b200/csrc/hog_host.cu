@@ -103,6 +103,7 @@ struct hogb200 {
     int device = 0;
     hogb200_geom g;
     // parameters (defaults hog.cpp:241-249)
+    BlockWeights weights;            // separable block window for win_sigma (recomputed by the setter)
     double win_sigma = -1.0, l2hys = 0.2; int gamma = 1; int nlevels = 64; double hit_threshold = 0.0;
     int win_stride_x = 8, win_stride_y = 8; double scale0 = 1.05; int group_threshold = 2;
     int descr_format = HOGB200_DESCR_FORMAT_COL_BY_COL;
@@ -517,7 +518,7 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
     if (h->timing) cudaEventRecord(h->ev[2], st);
     if (P.n_hist) {
         launch_hist(fs, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
-                    make_weights(h->win_sigma), (float)h->l2hys, h->d_hist.p, st);
+                    h->weights, (float)h->l2hys, h->d_hist.p, st);
         (*launches)++;
         g_watchdog.mark(st, "hist", nframes);
     }
@@ -673,16 +674,17 @@ size_t gpu_group_min()
     return v;
 }
 
-void group_rectangles_auto(hogb200* h, std::vector<hogb200_rect>& rects, int groupThreshold, double eps)
+// a CUDA failure of the device path is reported, never papered over by regrouping on the host
+int group_rectangles_auto(hogb200* h, std::vector<hogb200_rect>& rects, int groupThreshold, double eps)
 {
-    if (gpu_group_min() > 0 && rects.size() >= gpu_group_min() && group_rectangles_device(h, rects, groupThreshold, eps) == HOGB200_OK)
-        return;
+    if (gpu_group_min() > 0 && rects.size() >= gpu_group_min()) return group_rectangles_device(h, rects, groupThreshold, eps);
     group_rectangles(rects, groupThreshold, eps);
+    return HOGB200_OK;
 }
 
 // candidates of one (frame, detector), already in (level, y, x) order -> rects (hog.cpp:471-481) [+ grouping :484-487]
-void candidates_to_rects(hogb200* h, const Plan& P, const Candidate* c, size_t n,
-                         std::vector<hogb200_rect>& rects, std::vector<double>* conf)
+int candidates_to_rects(hogb200* h, const Plan& P, const Candidate* c, size_t n,
+                        std::vector<hogb200_rect>& rects, std::vector<double>* conf)
 {
     rects.clear();
     if (conf) conf->clear();
@@ -697,7 +699,8 @@ void candidates_to_rects(hogb200* h, const Plan& P, const Candidate* c, size_t n
         rects.push_back(r);
         if (conf) conf->push_back((double)c[i].score);
     }
-    if (h->group_threshold > 0) group_rectangles_auto(h, rects, h->group_threshold, 0.2);
+    if (h->group_threshold > 0) return group_rectangles_auto(h, rects, h->group_threshold, 0.2);
+    return HOGB200_OK;
 }
 
 void finish_timing(hogb200* h, const Plan& P, int launches, size_t ncand)
@@ -750,6 +753,7 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     if (device < 0 || device >= ndev) return fail(HOGB200_BAD_ARG, "bad device index");
     hogb200* h = new hogb200();
     h->device = device; h->g = g;
+    h->weights = make_weights(h->win_sigma);
     h->win_stride_x = g.block_stride_w; h->win_stride_y = g.block_stride_h;   // hog.cpp:246
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
@@ -805,16 +809,23 @@ int hogb200_set_stream(hogb200_t* h, void* s)
 }
 
 #define H_OR_FAIL if (!h) return fail(HOGB200_BAD_ARG, "null handle")
-int hogb200_set_win_sigma(hogb200_t* h, double v) { H_OR_FAIL; h->win_sigma = v; return HOGB200_OK; }
-double hogb200_get_win_sigma(const hogb200_t* h) { return h->win_sigma >= 0 ? h->win_sigma : (h->g.block_w + h->g.block_h) / 8.0; }
+// getters on a null handle return the reference's defaults (hog.cpp:241-249) instead of dereferencing it
+int hogb200_set_win_sigma(hogb200_t* h, double v) { H_OR_FAIL; h->win_sigma = v; h->weights = make_weights(v); return HOGB200_OK; }
+double hogb200_get_win_sigma(const hogb200_t* h) { return !h ? 4.0 : h->win_sigma >= 0 ? h->win_sigma : (h->g.block_w + h->g.block_h) / 8.0; }
 int hogb200_set_l2hys_threshold(hogb200_t* h, double v) { H_OR_FAIL; h->l2hys = v; return HOGB200_OK; }
-double hogb200_get_l2hys_threshold(const hogb200_t* h) { return h->l2hys; }
+double hogb200_get_l2hys_threshold(const hogb200_t* h) { return h ? h->l2hys : 0.2; }
 int hogb200_set_gamma_correction(hogb200_t* h, int v) { H_OR_FAIL; h->gamma = v != 0; return HOGB200_OK; }
-int hogb200_get_gamma_correction(const hogb200_t* h) { return h->gamma; }
-int hogb200_set_num_levels(hogb200_t* h, int v) { H_OR_FAIL; h->nlevels = v; return HOGB200_OK; }
-int hogb200_get_num_levels(const hogb200_t* h) { return h->nlevels; }
+int hogb200_get_gamma_correction(const hogb200_t* h) { return h ? h->gamma : 1; }
+int hogb200_set_num_levels(hogb200_t* h, int v)
+{
+    H_OR_FAIL;
+    // the reference takes any int and then forms scale 0 -> cvRound(W / 0.0) for nlevels <= 0 (hog.cpp:424-441): refused here
+    if (v < 1) return fail(HOGB200_BAD_ARG, "nlevels must be >= 1");
+    h->nlevels = v; return HOGB200_OK;
+}
+int hogb200_get_num_levels(const hogb200_t* h) { return h ? h->nlevels : 64; }
 int hogb200_set_hit_threshold(hogb200_t* h, double v) { H_OR_FAIL; h->hit_threshold = v; return HOGB200_OK; }
-double hogb200_get_hit_threshold(const hogb200_t* h) { return h->hit_threshold; }
+double hogb200_get_hit_threshold(const hogb200_t* h) { return h ? h->hit_threshold : 0.0; }
 int hogb200_set_win_stride(hogb200_t* h, int sx, int sy)
 {
     H_OR_FAIL;
@@ -822,11 +833,17 @@ int hogb200_set_win_stride(hogb200_t* h, int sx, int sy)
     h->win_stride_x = sx; h->win_stride_y = sy;     // divisibility is checked by the work calls, as hog.cpp:341,497 do
     return HOGB200_OK;
 }
-void hogb200_get_win_stride(const hogb200_t* h, int* sx, int* sy) { if (sx) *sx = h->win_stride_x; if (sy) *sy = h->win_stride_y; }
-int hogb200_set_scale_factor(hogb200_t* h, double v) { H_OR_FAIL; h->scale0 = v; return HOGB200_OK; }
-double hogb200_get_scale_factor(const hogb200_t* h) { return h->scale0; }
+void hogb200_get_win_stride(const hogb200_t* h, int* sx, int* sy) { if (sx) *sx = h ? h->win_stride_x : 8; if (sy) *sy = h ? h->win_stride_y : 8; }
+int hogb200_set_scale_factor(hogb200_t* h, double v)
+{
+    H_OR_FAIL;
+    // scale0 <= 1 is legal (one level, hog.cpp:433); zero, negative or non-finite factors only produce garbage sizes
+    if (!(v > 0) || !std::isfinite(v)) return fail(HOGB200_BAD_ARG, "scale factor must be positive and finite");
+    h->scale0 = v; return HOGB200_OK;
+}
+double hogb200_get_scale_factor(const hogb200_t* h) { return h ? h->scale0 : 1.05; }
 int hogb200_set_group_threshold(hogb200_t* h, int v) { H_OR_FAIL; h->group_threshold = v; return HOGB200_OK; }
-int hogb200_get_group_threshold(const hogb200_t* h) { return h->group_threshold; }
+int hogb200_get_group_threshold(const hogb200_t* h) { return h ? h->group_threshold : 2; }
 int hogb200_set_descriptor_format(hogb200_t* h, int v)
 {
     H_OR_FAIL;
@@ -834,8 +851,8 @@ int hogb200_set_descriptor_format(hogb200_t* h, int v)
         return fail(HOGB200_BAD_ARG, "Unknown descriptor format");
     h->descr_format = v; return HOGB200_OK;
 }
-int hogb200_get_descriptor_format(const hogb200_t* h) { return h->descr_format; }
-size_t hogb200_get_descriptor_size(const hogb200_t* h) { return (size_t)win_bx(h) * win_by(h) * kHist; }
+int hogb200_get_descriptor_format(const hogb200_t* h) { return h ? h->descr_format : HOGB200_DESCR_FORMAT_COL_BY_COL; }
+size_t hogb200_get_descriptor_size(const hogb200_t* h) { return h ? (size_t)win_bx(h) * win_by(h) * kHist : 0; }
 size_t hogb200_get_block_histogram_size(const hogb200_t*) { return kHist; }
 int hogb200_enable_timing(hogb200_t* h, int on) { H_OR_FAIL; h->timing = on != 0; return HOGB200_OK; }
 int hogb200_last_timings(const hogb200_t* h, hogb200_timings* out) { if (!h || !out) return fail(HOGB200_BAD_ARG, "null"); *out = h->last; return HOGB200_OK; }
@@ -886,7 +903,7 @@ int hogb200_create_from_file(const char* filename, const char* objname, int devi
     hogb200_t* h = nullptr;
     if ((rc = hogb200_create(&m.geom, device, &h))) return rc;
     // HOG_Impl::read (cudaobjdetect/src/hog.cpp:599-641): the stored parameters, defaults for the rest
-    h->win_sigma = m.win_sigma; h->l2hys = m.l2hys_threshold; h->gamma = m.gamma_correction; h->nlevels = m.nlevels;
+    h->win_sigma = m.win_sigma; h->weights = make_weights(m.win_sigma); h->l2hys = m.l2hys_threshold; h->gamma = m.gamma_correction; h->nlevels = m.nlevels;
     if (n && (rc = hogb200_set_svm_detector(h, 0, det.data(), n))) { hogb200_destroy(h); return rc; }
     *out = h;
     return HOGB200_OK;
@@ -895,6 +912,15 @@ int hogb200_create_from_file(const char* filename, const char* objname, int devi
 }  // extern "C"
 
 namespace {
+
+// what the SVM scoring kernel can take (svm.cu); checked before anything is queued, by every entry point that scores
+int check_svm_geometry(const hogb200* h)
+{
+    if (win_bx(h) != 7 && win_bx(h) != 5)
+        return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows 64 (7 blocks) or 48 (5 blocks) pixels wide");
+    if (win_by(h) > 15) return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows up to 128 pixels high");
+    return HOGB200_OK;
+}
 
 int check_work_params(const hogb200* h)
 {
@@ -940,9 +966,7 @@ int run_single(hogb200* h, Plan& P, const hogb200_image* img, bool single, int n
     if ((rc = check_work_params(h))) return rc;
     if ((rc = use_device(h))) return rc;
     if ((rc = build_plan(h, P, img->width, img->height, img->channels == 3 ? 4 : img->channels, single))) return rc;
-    if (ndet > 0 && win_bx(h) != 7 && win_bx(h) != 5)
-        return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows 64 (7 blocks) or 48 (5 blocks) pixels wide");
-    if (ndet > 0 && win_by(h) > 15) return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows up to 128 pixels high");
+    if (ndet > 0 && (rc = check_svm_geometry(h))) return rc;
     size_t cap = std::max<size_t>(h->cand_cap, 1 << 16);
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = ensure_cand(h, cap))) return rc;
@@ -1015,7 +1039,7 @@ int hogb200_detect_multiscale_slot(hogb200_t* h, int slot, const hogb200_image* 
         c.erase(std::remove_if(c.begin(), c.end(), [&](const Candidate& k) { return !((double)k.score >= h->hit_threshold); }), c.end());
     }
     std::vector<hogb200_rect> rects; std::vector<double> cf;
-    candidates_to_rects(h, h->plan, c.data(), c.size(), rects, conf ? &cf : nullptr);
+    if ((rc = candidates_to_rects(h, h->plan, c.data(), c.size(), rects, conf ? &cf : nullptr))) return rc;
     rc = emit(rects, found, capacity, count);
     if (rc == HOGB200_OK && conf && !cf.empty()) memcpy(conf, cf.data(), cf.size() * sizeof(double));
     return rc;
@@ -1035,6 +1059,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
     for (int d = 0; d < nslots; d++) if (!h->have_det[d]) return fail(HOGB200_BAD_ARG, "detector slot not set");
     int rc;
     if ((rc = check_work_params(h))) return rc;
+    if ((rc = check_svm_geometry(h))) return rc;
     if ((rc = use_device(h))) return rc;
     int slots[kMaxDet] = {0, 1, 2, 3};
     std::vector<hogb200_rect> all; all.reserve(1024);
@@ -1114,7 +1139,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
                 const int key = (i << 20) | (d << 16);
                 size_t e = pos;
                 while (e < c.size() && (c[e].level & ~0xffff) == key) e++;
-                candidates_to_rects(h, P, c.data() + pos, e - pos, rects, nullptr);
+                if ((rc = candidates_to_rects(h, P, c.data() + pos, e - pos, rects, nullptr))) return rc;
                 pos = e;
                 all.insert(all.end(), rects.begin(), rects.end());
                 offsets[++out_idx] = all.size();

@@ -16,9 +16,8 @@
 // world coordinates (never read by the tracker).
 #include "../../include/tbdb200.h"
 
-#include <emmintrin.h>
-
 #include <algorithm>
+#include <cmath>
 #include <map>
 #include <string>
 #include <utility>
@@ -31,8 +30,8 @@ int fail(const char* msg) { g_err = msg; return 1; }
 
 struct Box { int x, y, w, h; };
 
-// cv::saturate_cast<int>(double) = cvRound: CVTSD2SI under the default rounding mode (core/fast_math.hpp:200-214)
-inline int round_half_even(double v) { return _mm_cvtsd_si32(_mm_set_sd(v)); }
+// cv::saturate_cast<int>(double) = cvRound: round to nearest even under the default rounding mode (core/fast_math.hpp:200-214)
+inline int round_half_even(double v) { return (int)lrint(v); }
 
 // computeBoundingBoxOverlap (tbd.cpp:1083-1106)
 double iou(const Box& a, const Box& b)

@@ -21,14 +21,15 @@ def detect_sharded(detect_batch, frames, rank, world):
     return {i: np.asarray(r, np.int32).reshape(-1, 4) for i, r in zip(idx, out)}
 
 
-def gather_detections(local, n_frames, rank=0, world=1, dst=0):
+def gather_detections(local, n_frames, rank=0, world=1, dst=0, group=None):
     """Host gather of the per-frame box lists onto rank `dst` (torch.distributed.gather_object: pickled over the
-    process group's CPU path, a few KB per frame).  Returns the list in frame order on `dst`, None elsewhere."""
+    process group's CPU path, a few KB per frame; `group` = a gloo group when the default group is NCCL).
+    Returns the list in frame order on `dst`, None elsewhere."""
     if world == 1:
         return [local[i] for i in range(n_frames)]
     import torch.distributed as dist
     parts = [None] * world if rank == dst else None
-    dist.gather_object(local, parts, dst=dst)
+    dist.gather_object(local, parts, dst=dst, group=group)
     if rank != dst:
         return None
     merged = {}

@@ -4,8 +4,10 @@
 usage: python tools/ncu_traffic.py gpurun_out/prof_hist.ncu-rep > profiles/hist_kernel_traffic.json
 """
 import csv
+import hashlib
 import io
 import json
+import os
 import subprocess
 import sys
 
@@ -28,7 +30,11 @@ def main():
     def val(k):
         return float(d[k]) * UNIT.get(u[k], 1)
 
+    # the capture is only meaningful for the kernel source it was taken from: stamp it with `git hash-object hist.cu`
+    src = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "opencv_b200", "csrc", "hist.cu")
+    data = open(src, "rb").read()
     out = {"source": rep, "kernel": d["Kernel Name"][:80],
+           "source_hash": {"opencv_b200/csrc/hist.cu": hashlib.sha1(b"blob %d\0" % len(data) + data).hexdigest()},
            "dram_bytes_per_launch": val("dram__bytes_read.sum") + val("dram__bytes_write.sum"),
            "dram_read_bytes": val("dram__bytes_read.sum"), "dram_write_bytes": val("dram__bytes_write.sum"),
            "ncu": {"duration_us_under_ncu": float(d["gpu__time_duration.sum"]),
