@@ -88,9 +88,9 @@ struct Plan {
     std::vector<LevelHost> lv;
     long long hist_floats = 0, score_floats = 0, pyr_pixels = 0, nblocks = 0, nwindows = 0;
     size_t pyr_bytes = 0;
-    int n_resize = 0, n_hist = 0, n_svm = 0;
+    int n_resize = 0, n_hist = 0, n_svm = 0, n_svm2 = 0;
     DevBuf<LevelDesc> d_levels; DevBuf<ResizeCoef> d_xtab, d_ytab;
-    DevBuf<ResizeItem> d_ritems; DevBuf<HistItem> d_hitems; DevBuf<SvmItem> d_sitems;
+    DevBuf<ResizeItem> d_ritems; DevBuf<HistItem> d_hitems; DevBuf<SvmItem> d_sitems, d_sitems2;   // tiles of one-detector / two-detector scoring passes
     const uint8_t* pyr_base = nullptr;   // pyramid buffer the level pointers were built for
     bool valid = false;
 };
@@ -266,13 +266,15 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     if ((int)scales.size() > kMaxLevels) return fail(HOGB200_BAD_ARG, "too many pyramid levels (max 256)");
 
     const int wbx = win_bx(h), wby = win_by(h);
-    const int sbx = h->win_stride_x / kCell, sby = h->win_stride_y / kCell;
+    const bool svm_ok = svm_supports(wbx, wby);          // else the plan serves compute / blockHistograms only
+    const int tw1 = svm_ok ? svm_tile_wx(wbx, wby, 1) : 16, tw2 = 16;
+    const bool pass2 = svm_ok && svm_two_detector_pass(wbx, wby);
     P.lv.clear();
     P.hist_floats = P.score_floats = P.pyr_pixels = P.nblocks = P.nwindows = 0;
     size_t pyr = 0;
     std::vector<ResizeCoef> xtab, ytab;
-    std::vector<ResizeItem> ritems; std::vector<HistItem> hitems; std::vector<SvmItem> sitems;
-    std::vector<int> scost;
+    std::vector<ResizeItem> ritems; std::vector<HistItem> hitems; std::vector<SvmItem> sitems, sitems2;
+    std::vector<int> scost, scost2;
     std::vector<LevelDesc> descs;
     for (size_t i = 0; i < scales.size(); i++) {
         LevelHost L;
@@ -306,15 +308,19 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
         D.w = L.w; D.h = L.h; D.nbx = L.nbx; D.nby = L.nby; D.nwx = L.nwx; D.nwy = L.nwy;
         D.hist_off = L.hist_off; D.score_off = L.score_off; D.mode = L.mode; D.pitch = L.pitch;
         const int vwx = L.nbx - wbx + 1, vwy = L.nby - wby + 1;
-        if (L.nwx > 0 && vwx > 0 && vwy > 0)
-            for (int wy = 0; wy < vwy; wy += svm_tile_wy())
-                for (int wx = 0; wx < vwx; wx += svm_tile_wx()) {
+        if (svm_ok && L.nwx > 0 && vwx > 0 && vwy > 0)
+            for (int wy = 0; wy < vwy; wy += svm_tile_wy()) {
+                for (int wx = 0; wx < vwx; wx += tw1) {
                     sitems.push_back(SvmItem{(short)i, (short)wx, (short)wy, 0});
-                    scost.push_back(svm_tile_cost(vwx - wx, vwy - wy));
+                    scost.push_back(svm_tile_cost(vwx - wx, vwy - wy, tw1 > 16 && vwx - wx > 16 ? 2 : 1));
                 }
+                for (int wx = 0; pass2 && wx < vwx; wx += tw2) {
+                    sitems2.push_back(SvmItem{(short)i, (short)wx, (short)wy, 0});
+                    scost2.push_back(svm_tile_cost(vwx - wx, vwy - wy, 2));
+                }
+            }
         P.lv.push_back(L); descs.push_back(D);
     }
-    (void)sbx; (void)sby;
     // histogram work items: strips of P.strip block rows x tiles of 14 blocks, for every frame of the group;
     // the kernel's workers pull them from a queue, longest first, so that the tail is made of short ones
     P.strip = balance_strip(P.lv, group, h->num_sms * hist_workers_per_sm());
@@ -330,14 +336,15 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     });
     // SVM tiles are dealt round-robin to the persistent CTAs: most expensive first, so that the partly filled edge
     // tiles even out the tail
-    {
-        std::vector<int> order(sitems.size());
+    auto by_cost = [](std::vector<SvmItem>& items, const std::vector<int>& cost) {
+        std::vector<int> order(items.size());
         for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
-        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return scost[a] > scost[b]; });
-        std::vector<SvmItem> sorted; sorted.reserve(sitems.size());
-        for (int i : order) sorted.push_back(sitems[i]);
-        sitems.swap(sorted);
-    }
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
+        std::vector<SvmItem> sorted; sorted.reserve(items.size());
+        for (int i : order) sorted.push_back(items[i]);
+        items.swap(sorted);
+    };
+    by_cost(sitems, scost); by_cost(sitems2, scost2);
     // replicate the lists for frames 1 .. group-1 (frame-minor, so that equal-sized items of all frames are adjacent)
     if (group > 1) {
         std::vector<ResizeItem> r2; std::vector<HistItem> h2; std::vector<SvmItem> s2;
@@ -345,6 +352,9 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
         for (const HistItem& it : hitems) for (int f = 0; f < group; f++) { HistItem t = it; t.level = (short)(it.level | (f << 8)); h2.push_back(t); }
         for (const SvmItem& it : sitems) for (int f = 0; f < group; f++) { SvmItem t = it; t.frame = (short)f; s2.push_back(t); }
         ritems.swap(r2); hitems.swap(h2); sitems.swap(s2);
+        s2.clear();
+        for (const SvmItem& it : sitems2) for (int f = 0; f < group; f++) { SvmItem t = it; t.frame = (short)f; s2.push_back(t); }
+        sitems2.swap(s2);
     }
     P.pyr_stride = (long long)align_up(pyr, 256);
     P.hist_stride = P.hist_floats;
@@ -354,7 +364,7 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
         if (P.lv[i].mode != 0) descs[i].img = h->d_pyr.p + P.lv[i].img_off;
     P.pyr_base = h->d_pyr.p;
     CK(h->d_hist.reserve((size_t)P.hist_stride * group + 64));
-    P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size();
+    P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size(); P.n_svm2 = (int)sitems2.size();
     cudaStream_t st = h->stream;
     CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use
     auto up = [&](auto& buf, const auto& v) -> cudaError_t {
@@ -363,7 +373,7 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
         return cudaMemcpy(buf.p, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
     };
     CK(up(P.d_levels, descs)); CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
-    CK(up(P.d_ritems, ritems)); CK(up(P.d_hitems, hitems)); CK(up(P.d_sitems, sitems));
+    CK(up(P.d_ritems, ritems)); CK(up(P.d_hitems, hitems)); CK(up(P.d_sitems, sitems)); CK(up(P.d_sitems2, sitems2));
     P.valid = true;
     return HOGB200_OK;
 }
@@ -533,8 +543,8 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
         sp.cand = reinterpret_cast<Candidate*>(h->d_cand.p + 16);
         sp.cand_count = reinterpret_cast<unsigned int*>(h->d_cand.p);
         sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
-        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, h->d_hist.p, sp, h->num_sms, st);
-        (*launches)++;
+        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, P.d_sitems2.p, P.n_svm2, h->d_hist.p, sp, h->num_sms, st);
+        (*launches) += ndet >= 2 && P.n_svm2 ? (ndet + 1) / 2 : ndet;
         g_watchdog.mark(st, "svm", nframes);
     }
     if (h->timing) cudaEventRecord(h->ev[4], st);
@@ -790,7 +800,7 @@ void hogb200_destroy(hogb200_t* h)
     for (Plan& P : h->plan_part) plans.push_back(&P);
     for (Plan* P : plans) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
-        P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release();
+        P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release(); P->d_sitems2.release();
     }
     for (int i = 0; i < 2; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
     for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -916,9 +926,10 @@ namespace {
 // what the SVM scoring kernel can take (svm.cu); checked before anything is queued, by every entry point that scores
 int check_svm_geometry(const hogb200* h)
 {
-    if (win_bx(h) != 7 && win_bx(h) != 5)
-        return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows 64 (7 blocks) or 48 (5 blocks) pixels wide");
-    if (win_by(h) > 15) return fail(HOGB200_UNSUPPORTED, "SVM scoring supports windows up to 128 pixels high");
+    // any block-aligned window (hog.cpp:252-264) whose coefficient table leaves room for the histogram ring in shared
+    // memory: up to 21 blocks (176 px) wide and roughly 300 blocks in all (svm.cu, plan_pass)
+    if (!svm_supports(win_bx(h), win_by(h)))
+        return fail(HOGB200_UNSUPPORTED, "SVM scoring: window too large (more than 176 pixels wide or more than ~300 blocks)");
     return HOGB200_OK;
 }
 
@@ -1066,6 +1077,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
     offsets[0] = 0;
     size_t out_idx = 0;
     int total_launches = 0;
+    size_t total_cands = 0;
     const int kChunk = 64;
     std::vector<Candidate> c; std::vector<hogb200_rect> rects;
     cudaStream_t st = h->stream, cs = h->copy_stream;
@@ -1132,6 +1144,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
             if (rc) return rc;
             break;
         }
+        total_cands += c.size();
         std::sort(c.begin(), c.end(), cand_less);
         size_t pos = 0;
         for (int i = 0; i < nf; i++)
@@ -1147,7 +1160,7 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         f0 += nf;
     }
     if (h->timing) cudaEventRecord(h->ev[5], st);
-    finish_timing(h, h->plan_grp, total_launches, all.size());
+    finish_timing(h, h->plan_grp, total_launches, total_cands);
     size_t cnt = 0;
     return emit(all, found, capacity, &cnt);
 }

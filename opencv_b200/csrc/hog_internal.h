@@ -102,11 +102,15 @@ struct SvmParams {
     unsigned int cand_cap;
     int tag;                   // OR-ed into Candidate::level: frame-in-chunk << 20 (detector goes to bits 16..19)
 };
-void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
-                const SvmParams& p, int num_sms, cudaStream_t st);
-int svm_tile_wx();   // tile geometry the host uses to build SvmItems
+// items1 / items2: tile lists for passes scoring one detector (tiles svm_tile_wx(.., 1) windows wide) and two detectors
+// at once (16 wide); detectors are taken two per pass where the window geometry allows it
+void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items1, int nitems1,
+                const SvmItem* d_items2, int nitems2, const float* d_hist, const SvmParams& p, int num_sms, cudaStream_t st);
+bool svm_supports(int win_bx, int win_by);            // window geometries the scoring kernel takes (any up to 21 x ~14 blocks^2 of shared memory)
+bool svm_two_detector_pass(int win_bx, int win_by);
+int svm_tile_wx(int win_bx, int win_by, int ndet_pass);   // tile geometry the host uses to build SvmItems
 int svm_tile_wy();
-int svm_tile_cost(int cols_left, int rows_left);   // relative time of a tile with that many valid windows right / below its origin
+int svm_tile_cost(int cols_left, int rows_left, int units);   // relative time of a tile with that many valid windows right / below its origin
 
 void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_hist, int win_bx, int win_by,
                     int stride_bx, int stride_by, int col_by_col, float* d_out, cudaStream_t st);

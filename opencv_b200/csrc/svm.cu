@@ -10,14 +10,20 @@
 // the FP32 pipes (packed FFMA2), and the design goal is to keep that pipe issuing:
 //   * persistent kernel, one CTA per SM: 8 consumer warps (two per SM sub-partition -- FFMA2 throughput collapses
 //     when the sub-partitions hold unequal numbers of busy warps, tools/micro/probe2.cu) + 1 producer warp;
-//   * a tile is 32 x 32 windows of one level.  The producer streams the tile's 46 block rows (and then the next
-//     tile's) through a 39-slot shared-memory ring, one bulk async copy per row, signalling per-slot mbarriers;
-//   * a consumer warp owns 8 window rows x 16 window columns of the tile, for ALL of k: lane = (q, p), q = float4
-//     number 0..7 of the 36-float block histogram (k-split across the lanes of a quarter-warp, so its LDS.128 of
-//     a block is 128 contiguous bytes: conflict-free), p = pair of window rows.  The ninth float4 is shared out:
-//     lane q also handles it for windows q and q+8 of the 16.  A loaded histogram float4 feeds the 7 windows that
-//     contain the block in x times the 2 window rows that contain it in y, i.e. 28 FFMA2 per LDS.128, into
+//   * a tile is 32 window rows of one level, 32 windows wide for one detector or 16 wide for two detectors scored in
+//     the same pass.  The producer streams the tile's block rows (and then the next tile's) through a shared-memory
+//     ring, one bulk async copy per row, signalling per-slot mbarriers;
+//   * a consumer warp owns 8 window rows x 16 window columns of the tile for one detector, for ALL of k: the warps
+//     4..7 take the second column group (one detector) or the second detector (two): both detectors read the same
+//     ring rows, so the histograms cross shared memory once per pass whatever the number of detectors.
+//     lane = (q, p), q = float4 number 0..7 of the 36-float block histogram (k-split across the lanes of a
+//     quarter-warp, so its LDS.128 of a block is 128 contiguous bytes: conflict-free), p = pair of window rows.
+//     The ninth float4 is shared out: lane q also handles it for windows q and q+8 of the 16.  A loaded histogram
+//     float4 feeds the C windows that contain the block in x times the 2 window rows that contain it in y, into
 //     32 + 4 register accumulators (float2: even/odd k);
+//   * ANY window size: the window's WBX block columns are processed in `nchunks` chunks of C columns (C is the template
+//     parameter, 1..8; the coefficient table in shared memory is zero-padded to nchunks * C columns), WBY is a run-time
+//     loop bound.  64x128 and 48x96 are C = 7 / 5 with one chunk and no padding;
 //   * warps are coupled only through the ring: a warp waits for the one row each step adds and releases the row
 //     it read last, so the bands of a tile run staggered, the next tile's rows land while the current one is
 //     still being scored, and warps whose 8 x 16 windows lie outside the level only pass the tile's rows on;
@@ -36,23 +42,29 @@ constexpr int kCW = 8;                       // consumer warps
 constexpr int kConsumerThreads = kCW * 32;   // 256
 constexpr int kSvmThreads = kConsumerThreads + 32;           // + the producer warp
 constexpr int kT = 16;                       // adjacent windows per thread (x)
-constexpr int kBands = 4, kColGroups = 2;    // warp = (band of 8 window rows, group of 16 window columns)
+constexpr int kBands = 4;                    // warp = (band of 8 window rows, unit); unit = column group or detector
 constexpr int kBandRows = 8;
-constexpr int kTileWX = kColGroups * kT;     // 32
 constexpr int kTileWY = kBands * kBandRows;  // 32
-constexpr int kRing = 39;                    // a tile reads rows t .. t+31 at step t; the rest is prefetch depth
-constexpr int kMaxWBX = 7;
-constexpr int kRowBlocks = kTileWX + kMaxWBX - 1;          // 38
+constexpr int kRowBlocks = 38;                             // blocks a ring slot can hold
 constexpr int kRowFloats = 1376;                           // 43 x 128 B >= 38 blocks
 static_assert(kRowBlocks * kHist <= kRowFloats, "ring slot too small");
-constexpr int kMaxCoef = 7 * 15 * kHist;                   // 3780
+constexpr int kMaxRing = 64;                 // slots; a tile reads rows t .. t+31 at step t, the rest is prefetch depth
+constexpr int kMinRing = 34;
+constexpr int kBarBytes = 2 * kMaxRing * 8;  // full[] + empty[] mbarriers at the start of dynamic shared memory
+constexpr int kSmemBytes = 227 * 1024;
+constexpr int kMaxChunkC = 8;
 
-struct SvmSmem {
-    float ring[kRing][kRowFloats];                         // 214,656 B
-    float coef[kMaxCoef + 28];                             //  15,232 B
-    unsigned long long full[kRing], empty[kRing];          // mbarriers: row landed / row no longer read
+// how the kernel is laid out for one pass (filled by launch_svm)
+struct SvmPass {
+    int nchunks;        // column chunks of C blocks per window row (WBXp = nchunks * C >= win_bx)
+    int wbxp;           // padded window width in blocks
+    int tile_wx;        // 32 (one detector, two column groups) or 16
+    int two_det;        // warps 4..7 score the second detector of the pass instead of a second column group
+    int det_base;       // first detector slot of the pass
+    int ring;           // slots
+    int ncoefp;         // padded coefficients per detector: win_by * wbxp * 36
+    int zero_fill;      // padded columns multiply stale ring contents by zero: make sure they are finite
 };
-static_assert(sizeof(SvmSmem) <= 227 * 1024, "shared memory");
 
 // packed FP32 (Blackwell FFMA2): d = a * b + c on both halves
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c)
@@ -74,10 +86,6 @@ __device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count)
 __device__ __forceinline__ void mbar_arrive(unsigned mbar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_n(unsigned mbar, unsigned count)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(unsigned mbar, unsigned bytes)
 {
@@ -102,9 +110,6 @@ __device__ __forceinline__ bool mbar_test(unsigned mbar, unsigned parity)      /
         "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar), "r"(parity) : "memory");
     return ok != 0;
 }
-// slot / parity one position before (nslot, npar)
-__device__ __forceinline__ unsigned nslot_prev(unsigned nslot) { return nslot == 0 ? kRing - 1 : nslot - 1; }
-__device__ __forceinline__ unsigned npar_prev(unsigned nslot, unsigned npar) { return nslot == 0 ? npar ^ 1 : npar; }
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned mbar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -112,259 +117,282 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
 }
 // One step of a tile for one thread: block row `rowp` (the thread's first block) against coefficient row ca for
 // the upper window row of the pair (accA) and cb for the lower one (accB); A / B say which of the two window rows
-// contain this block row (the first step has no B, the last no A).
-template <int WBX, bool A, bool B>
+// contain this block row (the first step has no B, the last no A).  The window's columns come in `nchunks` chunks
+// of C blocks: chunk c of the coefficients meets the histograms C * c blocks further right.
+template <int C, bool A, bool B>
 __device__ __forceinline__ void svm_step(float2 (&accA)[kT], float2 (&accB)[kT], float2 (&exA)[2], float2 (&exB)[2],
                                          const float* __restrict__ ca, const float* __restrict__ cb,
-                                         const float* __restrict__ rowp, int q)
+                                         const float* __restrict__ rowp, int q, int nchunks)
 {
-    {   // float4 number q of every block, all 16 windows
-        float4 wa[WBX], wb[WBX];
+#pragma unroll 1
+    for (int ch = 0; ch < nchunks; ch++, ca += C * kHist, cb += C * kHist, rowp += C * kHist) {
+        {   // float4 number q of every block, all 16 windows
+            float4 wa[C], wb[C];
 #pragma unroll
-        for (int bx = 0; bx < WBX; bx++) {
-            if (A) wa[bx] = *reinterpret_cast<const float4*>(ca + bx * kHist + 4 * q);
-            if (B) wb[bx] = *reinterpret_cast<const float4*>(cb + bx * kHist + 4 * q);
-        }
+            for (int bx = 0; bx < C; bx++) {
+                if (A) wa[bx] = *reinterpret_cast<const float4*>(ca + bx * kHist + 4 * q);
+                if (B) wb[bx] = *reinterpret_cast<const float4*>(cb + bx * kHist + 4 * q);
+            }
 #pragma unroll
-        for (int X = 0; X < kT + WBX - 1; X++) {
-            const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist + 4 * q);
+            for (int X = 0; X < kT + C - 1; X++) {
+                const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist + 4 * q);
 #pragma unroll
-            for (int bx = 0; bx < WBX; bx++) {
-                const int j = X - bx;
-                if (j >= 0 && j < kT) {
-                    if (A) {
-                        accA[j] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), accA[j]);
-                        accA[j] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), accA[j]);
-                    }
-                    if (B) {
-                        accB[j] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), accB[j]);
-                        accB[j] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), accB[j]);
+                for (int bx = 0; bx < C; bx++) {
+                    const int j = X - bx;
+                    if (j >= 0 && j < kT) {
+                        if (A) {
+                            accA[j] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), accA[j]);
+                            accA[j] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), accA[j]);
+                        }
+                        if (B) {
+                            accB[j] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), accB[j]);
+                            accB[j] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), accB[j]);
+                        }
                     }
                 }
             }
         }
-    }
-    {   // the ninth float4 (floats 32..35): windows q and q + 8 only (lane q reads block q + bx: conflict-free)
-        float4 wa[WBX], wb[WBX];
+        {   // the ninth float4 (floats 32..35): windows q and q + 8 only (lane q reads block q + bx: conflict-free)
+            float4 wa[C], wb[C];
 #pragma unroll
-        for (int bx = 0; bx < WBX; bx++) {
-            if (A) wa[bx] = *reinterpret_cast<const float4*>(ca + bx * kHist + 32);
-            if (B) wb[bx] = *reinterpret_cast<const float4*>(cb + bx * kHist + 32);
-        }
-        const float* r8 = rowp + q * kHist + 32;
+            for (int bx = 0; bx < C; bx++) {
+                if (A) wa[bx] = *reinterpret_cast<const float4*>(ca + bx * kHist + 32);
+                if (B) wb[bx] = *reinterpret_cast<const float4*>(cb + bx * kHist + 32);
+            }
+            const float* r8 = rowp + q * kHist + 32;
 #pragma unroll
-        for (int e = 0; e < 2; e++) {
+            for (int e = 0; e < 2; e++) {
 #pragma unroll
-            for (int bx = 0; bx < WBX; bx++) {
-                const float4 hv = *reinterpret_cast<const float4*>(r8 + (8 * e + bx) * kHist);
-                if (A) {
-                    exA[e] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), exA[e]);
-                    exA[e] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), exA[e]);
-                }
-                if (B) {
-                    exB[e] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), exB[e]);
-                    exB[e] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), exB[e]);
+                for (int bx = 0; bx < C; bx++) {
+                    const float4 hv = *reinterpret_cast<const float4*>(r8 + (8 * e + bx) * kHist);
+                    if (A) {
+                        exA[e] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), exA[e]);
+                        exA[e] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), exA[e]);
+                    }
+                    if (B) {
+                        exB[e] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), exB[e]);
+                        exB[e] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), exB[e]);
+                    }
                 }
             }
         }
     }
 }
 
-// `n` numbers the rows pushed through the ring since the kernel started; slot = n % kRing and the mbarrier phase
-// parity is (n / kRing) & 1 on both the producer and the consumer side.
+// `n` numbers the rows pushed through the ring since the kernel started; slot = n % ring and the mbarrier phase
+// parity is (n / ring) & 1 on both the producer and the consumer side.
 //   full[slot]   producer -> consumers: the row's bytes have landed (expect_tx / complete_tx)
 //   empty[slot]  consumers -> producer: all 8 warps are done with the row (a warp also waits for and releases the
 //                rows it does not read)
-template <int WBX>
+template <int C>
 __global__ void __launch_bounds__(kSvmThreads, 1)
 svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
-           int nitems, const float* __restrict__ hist, const __grid_constant__ SvmParams P)
+           int nitems, const float* __restrict__ hist, const __grid_constant__ SvmParams P, const __grid_constant__ SvmPass S)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    SvmSmem& s = *reinterpret_cast<SvmSmem*>(smem_raw);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31;
     const bool producer = tid >= kConsumerThreads;
-    const unsigned full0 = smem_u32(&s.full[0]), empty0 = smem_u32(&s.empty[0]);
+    const int ring = S.ring;
+    const unsigned full0 = smem_u32(smem_raw), empty0 = full0 + 8 * kMaxRing;
+    float* const coef = reinterpret_cast<float*>(smem_raw + kBarBytes);
+    const int ndet_pass = S.two_det ? 2 : 1;
+    const unsigned coef_bytes = ((unsigned)(ndet_pass * S.ncoefp) * 4u + 127u) & ~127u;
+    float* const ringp = reinterpret_cast<float*>(smem_raw + kBarBytes + coef_bytes);
     if (tid == 0) {
-        for (int i = 0; i < kRing; i++) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, kCW); }
+        for (int i = 0; i < ring; i++) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, kCW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    const int win_by = P.win_by;
-    const int ncoef = win_by * WBX * kHist;
+    const int win_by = P.win_by, win_bx = P.win_bx, wbxp = S.wbxp;
     const int tile_rows = kTileWY + win_by - 1;
+    // the detectors of this pass, [detector][block row][padded block column][36], columns >= win_bx are zero
+    for (int d = 0; d < ndet_pass; d++) {
+        const float4* __restrict__ src = reinterpret_cast<const float4*>(P.det[S.det_base + d]);
+        float4* dst = reinterpret_cast<float4*>(coef + d * S.ncoefp);
+        for (int i = tid; i < S.ncoefp / 4; i += kSvmThreads) {
+            const int blk = i / 9, k4 = i - blk * 9;
+            const int by = blk / wbxp, bx = blk - by * wbxp;
+            dst[i] = bx < win_bx ? __ldg(src + (by * win_bx + bx) * 9 + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    if (S.zero_fill)
+        for (int i = tid; i < ring * (kRowFloats / 4); i += kSvmThreads) reinterpret_cast<float4*>(ringp)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();     // barriers initialised, coefficients in place
     unsigned n = 0;
 
-    for (int d = 0; d < P.ndet; d++) {
-        __syncthreads();     // barriers initialised / everyone is done with the previous detector
-        for (int i = tid; i < ncoef / 4; i += kSvmThreads)
-            reinterpret_cast<float4*>(s.coef)[i] = __ldg(reinterpret_cast<const float4*>(P.det[d]) + i);
-        __syncthreads();
-
-        if (producer) {
-            // every lane streams its own rows (lane, lane + 32 of each tile): the waits for free slots overlap, so the
-            // 30-odd rows that become loadable at once when a tile ends are issued back to back
-            const unsigned ring0 = smem_u32(&s.ring[0][0]);
-            for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
-                const SvmItem it = items[ii];
-                if (it.frame >= fs.nframes) continue;
-                const LevelDesc& L = levels[it.level];
-                const int nbx = L.nbx, nby = L.nby;
-                const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
-                const unsigned bytes = (unsigned)max(0, min(kRowBlocks, nbx - it.wx0)) * (kHist * 4);
-                for (int r0 = 0; r0 < tile_rows; r0 += 32) {
-                    const int r = r0 + lane;
-                    if (r < tile_rows) {
-                        const unsigned m = n + r, slot = m % kRing, use = m / kRing;
-                        if (use > 0) mbar_wait(empty0 + 8 * slot, (use - 1) & 1);
-                        const int by_abs = it.wy0 + r;
-                        if (by_abs < nby && bytes > 0) {         // rows below the level feed only discarded windows
-                            mbar_expect_tx(full0 + 8 * slot, bytes);
-                            bulk_g2s(ring0 + slot * (kRowFloats * 4),
-                                     plane + ((long long)by_abs * nbx + it.wx0) * kHist, bytes, full0 + 8 * slot);
-                        } else {
-                            mbar_arrive(full0 + 8 * slot);
-                        }
-                    }
-                    // lanes stay within 32 < kRing positions of each other: a parity wait on a slot is only sound
-                    // once the slot's previous use has been issued
-                    __syncwarp();
-                }
-                n += tile_rows;
-            }
-            __syncwarp();
-            continue;
-        }
-
-        // ---- consumers: warp w sits on sub-partition w % 4; (band + 2 * colgroup) % 4 == w % 4 keeps the
-        // sub-partitions evenly loaded when the lower bands or the right column group of a tile are outside the level
-        const int w = tid >> 5;
-        const int cg = w >> 2, band = cg ? ((w - 2) & 3) : w;
-        const int q = lane & 7, pr = lane >> 3;
+    if (producer) {
+        // every lane streams its own rows (lane, lane + 32 of each tile): the waits for free slots overlap, so the
+        // 30-odd rows that become loadable at once when a tile ends are issued back to back
+        if (S.zero_fill) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy zeros before async-proxy writes
+        const unsigned ring0 = smem_u32(ringp);
+        const int row_blocks = min(kRowBlocks, S.tile_wx + win_bx - 1);
         for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
             const SvmItem it = items[ii];
             if (it.frame >= fs.nframes) continue;
             const LevelDesc& L = levels[it.level];
-            const int vwx = L.nbx - WBX + 1, vwy = L.nby - win_by + 1;   // dense (stride-1) window grid of the level
-            const int wx0 = it.wx0 + cg * kT, wy0 = it.wy0 + band * kBandRows;
-            // Every warp waits for and releases EVERY row of every tile, in ring order, also the rows (and the whole
-            // tiles) it does not read: a parity wait on a slot is only sound for a warp that released the slot's
-            // previous use, and the slot cannot be reused twice behind the back of a warp that still owes a release.
-            const unsigned tile0 = n, pos0 = n + band * kBandRows;      // ring position of the tile's / the band's first row
-            n += tile_rows;
-            const int rest = tile_rows - (band * kBandRows + 7 + win_by);   // rows below the band's last one
-            if (wx0 >= vwx || wy0 >= vwy) {                             // nothing to score here
-                // Rows 39.. of a tile reuse the slots of its rows 0..: a lane may only test a slot's NEXT use once the
-                // slot's current use is known to have landed (a parity test cannot tell "not yet" from "one phase
-                // ago"), and rows land out of order.  Hence the warp-wide join between the two rounds.
-                for (int r0 = 0; r0 < tile_rows; r0 += 32) {
-                    const unsigned m = tile0 + r0 + lane;
-                    if (r0 + lane < tile_rows) {
-                        mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
-                        mbar_arrive(empty0 + 8 * (m % kRing));
+            const int nbx = L.nbx, nby = L.nby;
+            const float* plane = hist + it.frame * fs.hist_stride + L.hist_off;
+            const unsigned bytes = (unsigned)max(0, min(row_blocks, nbx - it.wx0)) * (kHist * 4);
+            for (int r0 = 0; r0 < tile_rows; r0 += 32) {
+                const int r = r0 + lane;
+                if (r < tile_rows) {
+                    const unsigned m = n + r, slot = m % ring, use = m / ring;
+                    if (use > 0) mbar_wait(empty0 + 8 * slot, (use - 1) & 1);
+                    const int by_abs = it.wy0 + r;
+                    if (by_abs < nby && bytes > 0) {         // rows below the level feed only discarded windows
+                        mbar_expect_tx(full0 + 8 * slot, bytes);
+                        bulk_g2s(ring0 + slot * (kRowFloats * 4),
+                                 plane + ((long long)by_abs * nbx + it.wx0) * kHist, bytes, full0 + 8 * slot);
+                    } else {
+                        mbar_arrive(full0 + 8 * slot);
                     }
-                    __syncwarp();
                 }
-                continue;
+                // lanes stay within 32 < ring positions of each other: a parity wait on a slot is only sound
+                // once the slot's previous use has been issued
+                __syncwarp();
             }
-            if (lane < band * kBandRows + 7) {                          // the rows above the band + the 7 rows steps 0 and 1 read
-                const unsigned m = tile0 + lane;
-                mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
-                if (lane < band * kBandRows) mbar_arrive(empty0 + 8 * (m % kRing));
-            }
-            __syncwarp();
+            n += tile_rows;
+        }
+        return;
+    }
 
-            float2 accA[kT], accB[kT], exA[2], exB[2];    // (even k, odd k) partial sums of window rows 2pr / 2pr+1
-#pragma unroll
-            for (int j = 0; j < kT; j++) accA[j] = accB[j] = make_float2(0.f, 0.f);
-            exA[0] = exA[1] = exB[0] = exB[1] = make_float2(0.f, 0.f);
-            unsigned slot_l = (pos0 + 2 * pr) % kRing;
-            unsigned oslot = pos0 % kRing;                               // slot of the band's oldest live row
-            unsigned nslot = (pos0 + kBandRows - 1) % kRing;             // slot / parity of the row the NEXT step adds
-            unsigned npar = ((pos0 + kBandRows - 1) / kRing) & 1;
-            bool ready = true;
-            for (int t = 0; t <= win_by; t++) {
-                if (!ready) mbar_wait(full0 + 8 * nslot_prev(nslot), npar_prev(nslot, npar));
-                // poll the next step's row now, so that the answer is there when this step's arithmetic is done
-                ready = t == win_by || mbar_test(full0 + 8 * nslot, npar);
-                const float* rowp = &s.ring[slot_l][cg * kT * kHist];
-                const float* ca = s.coef + t * (WBX * kHist);
-                const float* cb = ca - WBX * kHist;
-                if (t == 0) svm_step<WBX, true, false>(accA, accB, exA, exB, ca, cb, rowp, q);
-                else if (t == win_by) svm_step<WBX, false, true>(accA, accB, exA, exB, ca, cb, rowp, q);
-                else svm_step<WBX, true, true>(accA, accB, exA, exB, ca, cb, rowp, q);
-                __syncwarp();                                           // every lane has read row pos0 + t for the last time
-                if (lane == 0) mbar_arrive(empty0 + 8 * oslot);
-                slot_l = slot_l + 1 == kRing ? 0 : slot_l + 1;
-                oslot = oslot + 1 == kRing ? 0 : oslot + 1;
-                if (++nslot == kRing) { nslot = 0; npar ^= 1; }
+    // ---- consumers: warp w sits on sub-partition w % 4; (band + 2 * unit) % 4 == w % 4 keeps the
+    // sub-partitions evenly loaded when the lower bands or the second unit of a tile have nothing to score
+    const int w = tid >> 5;
+    const int unit = w >> 2, band = unit ? ((w - 2) & 3) : w;
+    const int cg = S.two_det ? 0 : unit;                     // column group of the tile
+    const int det = S.two_det ? unit : 0;                    // detector of the pass
+    const bool unit_live = S.two_det || cg * kT < S.tile_wx;
+    const int dslot = S.det_base + det;
+    const float* const mycoef = coef + det * S.ncoefp;
+    const int crow = wbxp * kHist;                           // floats per coefficient row
+    const int q = lane & 7, pr = lane >> 3;
+    for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
+        const SvmItem it = items[ii];
+        if (it.frame >= fs.nframes) continue;
+        const LevelDesc& L = levels[it.level];
+        const int vwx = L.nbx - win_bx + 1, vwy = L.nby - win_by + 1;   // dense (stride-1) window grid of the level
+        const int wx0 = it.wx0 + cg * kT, wy0 = it.wy0 + band * kBandRows;
+        // Every warp waits for and releases EVERY row of every tile, in ring order, also the rows (and the whole
+        // tiles) it does not read: a parity wait on a slot is only sound for a warp that released the slot's
+        // previous use, and the slot cannot be reused twice behind the back of a warp that still owes a release.
+        const unsigned tile0 = n, pos0 = n + band * kBandRows;      // ring position of the tile's / the band's first row
+        n += tile_rows;
+        const int rest = tile_rows - (band * kBandRows + 7 + win_by);   // rows below the band's last one
+        if (!unit_live || wx0 >= vwx || wy0 >= vwy) {               // nothing to score here
+            // Rows `ring`.. of a tile reuse the slots of its rows 0..: a lane may only test a slot's NEXT use once the
+            // slot's current use is known to have landed (a parity test cannot tell "not yet" from "one phase
+            // ago"), and rows land out of order.  Hence the warp-wide join between the rounds.
+            for (int r0 = 0; r0 < tile_rows; r0 += 32) {
+                const unsigned m = tile0 + r0 + lane;
+                if (r0 + lane < tile_rows) {
+                    mbar_wait(full0 + 8 * (m % ring), (m / ring) & 1);
+                    mbar_arrive(empty0 + 8 * (m % ring));
+                }
+                __syncwarp();
             }
-            if (lane < kBandRows - 2) mbar_arrive(empty0 + 8 * ((pos0 + win_by + 1 + lane) % kRing));   // the band's last 6 rows
+            continue;
+        }
+        if (lane < band * kBandRows + 7) {                          // the rows above the band + the 7 rows steps 0 and 1 read
+            const unsigned m = tile0 + lane;
+            mbar_wait(full0 + 8 * (m % ring), (m / ring) & 1);
+            if (lane < band * kBandRows) mbar_arrive(empty0 + 8 * (m % ring));
+        }
+        __syncwarp();
 
-            // ---- the 8 lanes of a quarter-warp hold the k-partials of the same 2 x 16 windows: reduce-scatter
-            float v[2 * kT];
+        float2 accA[kT], accB[kT], exA[2], exB[2];    // (even k, odd k) partial sums of window rows 2pr / 2pr+1
 #pragma unroll
-            for (int j = 0; j < kT; j++) {
-                v[j] = accA[j].x + accA[j].y;
-                v[kT + j] = accB[j].x + accB[j].y;
-                if ((j & 7) == q) {
-                    v[j] += exA[j >> 3].x + exA[j >> 3].y;
-                    v[kT + j] += exB[j >> 3].x + exB[j >> 3].y;
-                }
+        for (int j = 0; j < kT; j++) accA[j] = accB[j] = make_float2(0.f, 0.f);
+        exA[0] = exA[1] = exB[0] = exB[1] = make_float2(0.f, 0.f);
+        unsigned slot_l = (pos0 + 2 * pr) % ring;
+        unsigned oslot = pos0 % ring;                                // slot of the band's oldest live row
+        unsigned nslot = (pos0 + kBandRows - 1) % ring;              // slot / parity of the row the NEXT step adds
+        unsigned npar = ((pos0 + kBandRows - 1) / ring) & 1;
+        bool ready = true;
+        for (int t = 0; t <= win_by; t++) {
+            if (!ready) {                                            // the row this step adds: one position before (nslot, npar)
+                const unsigned ps = nslot == 0 ? ring - 1 : nslot - 1, pp = nslot == 0 ? npar ^ 1 : npar;
+                mbar_wait(full0 + 8 * ps, pp);
             }
-            float v4[4];
-            {
-                const bool h4 = q & 4, h2 = q & 2, h1 = q & 1;
-                float v16[16], v8[8];
+            // poll the next step's row now, so that the answer is there when this step's arithmetic is done
+            ready = t == win_by || mbar_test(full0 + 8 * nslot, npar);
+            const float* rowp = ringp + slot_l * kRowFloats + cg * kT * kHist;
+            const float* ca = mycoef + t * crow;
+            const float* cb = ca - crow;
+            if (t == 0) svm_step<C, true, false>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            else if (t == win_by) svm_step<C, false, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            else svm_step<C, true, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            __syncwarp();                                           // every lane has read row pos0 + t for the last time
+            if (lane == 0) mbar_arrive(empty0 + 8 * oslot);
+            slot_l = slot_l + 1 == ring ? 0 : slot_l + 1;
+            oslot = oslot + 1 == ring ? 0 : oslot + 1;
+            if (++nslot == ring) { nslot = 0; npar ^= 1; }
+        }
+        if (lane < kBandRows - 2) mbar_arrive(empty0 + 8 * ((pos0 + win_by + 1 + lane) % ring));   // the band's last 6 rows
+
+        // ---- the 8 lanes of a quarter-warp hold the k-partials of the same 2 x 16 windows: reduce-scatter
+        float v[2 * kT];
 #pragma unroll
-                for (int i = 0; i < 16; i++) {
-                    const float snd = h4 ? v[i] : v[16 + i], keep = h4 ? v[16 + i] : v[i];
-                    v16[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 4);
-                }
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    const float snd = h2 ? v16[i] : v16[8 + i], keep = h2 ? v16[8 + i] : v16[i];
-                    v8[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 2);
-                }
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const float snd = h1 ? v8[i] : v8[4 + i], keep = h1 ? v8[4 + i] : v8[i];
-                    v4[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 1);
-                }
+        for (int j = 0; j < kT; j++) {
+            v[j] = accA[j].x + accA[j].y;
+            v[kT + j] = accB[j].x + accB[j].y;
+            if ((j & 7) == q) {
+                v[j] += exA[j >> 3].x + exA[j >> 3].y;
+                v[kT + j] += exB[j >> 3].x + exB[j >> 3].y;
             }
-            // lane (q, pr) now owns window row 2pr + (q >> 2), windows 8 * ((q >> 1) & 1) + 4 * (q & 1) .. + 3
-            const int vy = wy0 + 2 * pr + (q >> 2);
-            const int vxb = wx0 + 8 * ((q >> 1) & 1) + 4 * (q & 1);
-            const bool row_ok = vy < vwy && (vy % P.stride_by == 0);
-            const int oy = vy / P.stride_by;
+        }
+        float v4[4];
+        {
+            const bool h4 = q & 4, h2 = q & 2, h1 = q & 1;
+            float v16[16], v8[8];
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const float snd = h4 ? v[i] : v[16 + i], keep = h4 ? v[16 + i] : v[i];
+                v16[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 4);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const float snd = h2 ? v16[i] : v16[8 + i], keep = h2 ? v16[8 + i] : v16[i];
+                v8[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 2);
+            }
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const float sc = v4[i] + P.bias[d];
-                const int vx = vxb + i;
-                const bool valid = row_ok && vx < vwx && (vx % P.stride_bx == 0);
-                const int ox = vx / P.stride_bx;
-                if (valid && P.scores) P.scores[d * P.score_plane + L.score_off + (long long)oy * L.nwx + ox] = sc;
-                const bool hit = valid && sc >= P.thresh;
-                const unsigned m = __ballot_sync(0xffffffffu, hit);
-                if (m) {
-                    unsigned base = 0;
-                    if (lane == 0) base = atomicAdd(P.cand_count, __popc(m));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (hit) {
-                        const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
-                        if (pos < P.cand_cap) {
-                            Candidate c2; c2.level = it.level | (d << 16) | (P.tag + (it.frame << 20)); c2.x = ox; c2.y = oy; c2.score = sc;
-                            P.cand[pos] = c2;
-                        }
+                const float snd = h1 ? v8[i] : v8[4 + i], keep = h1 ? v8[4 + i] : v8[i];
+                v4[i] = keep + __shfl_xor_sync(0xffffffffu, snd, 1);
+            }
+        }
+        // lane (q, pr) now owns window row 2pr + (q >> 2), windows 8 * ((q >> 1) & 1) + 4 * (q & 1) .. + 3
+        const int vy = wy0 + 2 * pr + (q >> 2);
+        const int vxb = wx0 + 8 * ((q >> 1) & 1) + 4 * (q & 1);
+        const bool row_ok = vy < vwy && (vy % P.stride_by == 0);
+        const int oy = vy / P.stride_by;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float sc = v4[i] + P.bias[dslot];
+            const int vx = vxb + i;
+            const bool valid = row_ok && vx < vwx && (vx % P.stride_bx == 0);
+            const int ox = vx / P.stride_bx;
+            if (valid && P.scores) P.scores[dslot * P.score_plane + L.score_off + (long long)oy * L.nwx + ox] = sc;
+            const bool hit = valid && sc >= P.thresh;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (m) {
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(P.cand_count, __popc(m));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (hit) {
+                    const unsigned pos = base + __popc(m & ((1u << lane) - 1u));
+                    if (pos < P.cand_cap) {
+                        Candidate c2; c2.level = it.level | (dslot << 16) | (P.tag + (it.frame << 20)); c2.x = ox; c2.y = oy; c2.score = sc;
+                        P.cand[pos] = c2;
                     }
                 }
             }
-            if (lane < rest) {                                          // rows of the tile below the band
-                const unsigned m = pos0 + 7 + win_by + lane;
-                mbar_wait(full0 + 8 * (m % kRing), (m / kRing) & 1);
-                mbar_arrive(empty0 + 8 * (m % kRing));
-            }
-            __syncwarp();
         }
+        if (lane < rest) {                                          // rows of the tile below the band
+            const unsigned m = pos0 + 7 + win_by + lane;
+            mbar_wait(full0 + 8 * (m % ring), (m / ring) & 1);
+            mbar_arrive(empty0 + 8 * (m % ring));
+        }
+        __syncwarp();
     }
 }
 
@@ -390,32 +418,106 @@ __global__ void extract_kernel(const LevelDesc* __restrict__ level, const float*
 
 }  // namespace
 
-int svm_tile_wx() { return kTileWX; }
-int svm_tile_wy() { return kTileWY; }
-int svm_tile_cost(int cols_left, int rows_left)
+// ---- pass geometry (host) ---------------------------------------------------------------------------
+// column chunking of a window WBX blocks wide: (C, nchunks) with nchunks * C >= WBX, C <= 8, least padding
+static void chunking(int wbx, int* C, int* nchunks)
 {
-    // a warp = (band, column group) works only if its 8 x 16 windows intersect the level; the tile takes as long as
-    // the busiest sub-partition, which hosts (band s, group 0) and (band (s + 2) % 4, group 1)
-    const int nb = std::min(kBands, (rows_left + kBandRows - 1) / kBandRows), nc = cols_left > kT ? 2 : 1;
+    *nchunks = (wbx + kMaxChunkC - 1) / kMaxChunkC;
+    *C = (wbx + *nchunks - 1) / *nchunks;
+}
+
+static bool plan_pass(int win_bx, int win_by, int ndet_pass, SvmPass* S, int* C)
+{
+    int c, nch;
+    chunking(win_bx, &c, &nch);
+    const int wbxp = c * nch;
+    if (kT + wbxp - 1 > kRowBlocks) return false;                     // a 16-window column group must fit a ring slot
+    const long long ncoefp = (long long)win_by * wbxp * kHist;
+    const long long coef_bytes = ((ndet_pass * ncoefp * 4) + 127) / 128 * 128;
+    const long long ring = (kSmemBytes - kBarBytes - coef_bytes) / (kRowFloats * 4);
+    if (ring < kMinRing) return false;
+    S->nchunks = nch; S->wbxp = wbxp;
+    S->two_det = ndet_pass == 2;
+    S->tile_wx = (ndet_pass == 1 && 2 * kT + wbxp - 1 <= kRowBlocks) ? 2 * kT : kT;
+    S->det_base = 0;
+    S->ring = (int)std::min<long long>(ring, kMaxRing);
+    S->ncoefp = (int)ncoefp;
+    S->zero_fill = wbxp != win_bx;
+    *C = c;
+    return true;
+}
+
+bool svm_supports(int win_bx, int win_by)
+{
+    SvmPass S; int C;
+    return win_bx >= 1 && win_by >= 1 && plan_pass(win_bx, win_by, 1, &S, &C);
+}
+bool svm_two_detector_pass(int win_bx, int win_by)
+{
+    SvmPass S; int C;
+    return plan_pass(win_bx, win_by, 2, &S, &C);
+}
+int svm_tile_wx(int win_bx, int win_by, int ndet_pass)
+{
+    SvmPass S; int C;
+    return plan_pass(win_bx, win_by, ndet_pass, &S, &C) ? S.tile_wx : kT;
+}
+int svm_tile_wy() { return kTileWY; }
+int svm_tile_cost(int cols_left, int rows_left, int units)
+{
+    // a warp = (band, unit) works only if its 8 x 16 windows intersect the level (a second DETECTOR always has the
+    // same windows as the first); the tile takes as long as the busiest sub-partition, which hosts (band s, unit 0)
+    // and (band (s + 2) % 4, unit 1)
+    const int nb = std::min(kBands, (rows_left + kBandRows - 1) / kBandRows);
     int busiest = 0, total = 0;
     for (int sp = 0; sp < 4; sp++) {
-        const int a = (sp < nb) + (nc > 1 && ((sp + 2) & 3) < nb);
+        const int a = (sp < nb) + (units > 1 && ((sp + 2) & 3) < nb);
         busiest = std::max(busiest, a); total += a;
     }
+    (void)cols_left;
     return busiest * 16 + total;
 }
 
-void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
-                const SvmParams& p, int num_sms, cudaStream_t st)
+template <int C>
+static void launch_pass(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
+                        const SvmParams& p, const SvmPass& S, int grid, cudaStream_t st)
 {
-    if (nitems <= 0 || p.ndet <= 0) return;
-    const int grid = std::max(1, std::min(num_sms, nitems));
-    if (p.win_bx == 7) {
-        cudaFuncSetAttribute(svm_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<7><<<grid, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, nitems, d_hist, p);
-    } else if (p.win_bx == 5) {
-        cudaFuncSetAttribute(svm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SvmSmem));
-        svm_kernel<5><<<grid, kSvmThreads, sizeof(SvmSmem), st>>>(fs, d_levels, d_items, nitems, d_hist, p);
+    // the opt-in shared-memory size is a per-device function attribute: set once per device, not per launch
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63])
+        attr_set[dev & 63] = cudaFuncSetAttribute(svm_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) == cudaSuccess;
+    svm_kernel<C><<<grid, kSvmThreads, kSmemBytes, st>>>(fs, d_levels, d_items, nitems, d_hist, p, S);
+}
+
+// items1 / items2: the tile lists for one-detector passes (svm_tile_wx(.., 1) wide) and two-detector passes (16 wide)
+void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items1, int nitems1,
+                const SvmItem* d_items2, int nitems2, const float* d_hist, const SvmParams& p, int num_sms, cudaStream_t st)
+{
+    if (p.ndet <= 0) return;
+    const bool can2 = svm_two_detector_pass(p.win_bx, p.win_by) && nitems2 > 0;
+    for (int d = 0; d < p.ndet;) {
+        const int nd = (p.ndet - d >= 2 && can2) ? 2 : 1;
+        SvmPass S; int C = 0;
+        if (!plan_pass(p.win_bx, p.win_by, nd, &S, &C)) return;        // refused earlier by the host (svm_supports)
+        S.det_base = d;
+        const SvmItem* items = nd == 2 ? d_items2 : d_items1;
+        const int nitems = nd == 2 ? nitems2 : nitems1;
+        if (nitems > 0) {
+            const int grid = std::max(1, std::min(num_sms, nitems));
+            switch (C) {
+                case 1: launch_pass<1>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 2: launch_pass<2>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 3: launch_pass<3>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 4: launch_pass<4>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 5: launch_pass<5>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 6: launch_pass<6>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                case 7: launch_pass<7>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                default: launch_pass<8>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+            }
+        }
+        d += nd;
     }
 }
 

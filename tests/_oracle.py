@@ -279,3 +279,30 @@ def synthetic_frame(seed, w, h, cn, blur=True, silhouettes=0):
     if cn == 4:
         img = np.concatenate([img, np.full((h, w, 1), 255, np.uint8)], axis=2)
     return np.ascontiguousarray(img)
+
+
+SCORE_TOL = 1e-3
+
+
+def detections_match(hog, port, img, det, hit, group, scale0=1.05, nlevels=64, slot=0, g=DEFAULT_GEOM, win_stride=(8, 8)):
+    """The north-star bar for detectMultiScale: the GPU's grouped set equals the oracle's, except for windows whose
+    score lies within SCORE_TOL of the hit threshold.  When the two differ, (1) the GPU's UNGROUPED candidate set must
+    lie between the oracle's sets at hit +/- SCORE_TOL (only near-threshold windows may differ), and (2) the GPU's
+    grouped output must be exactly what the oracle's groupRectangles makes of the GPU's own candidate list -- so the
+    grouped output is verified in both cases.  -> (ok, got, exp); leaves hit/group thresholds set on `hog`."""
+    hog.setHitThreshold(hit); hog.setGroupThreshold(group); hog.setScaleFactor(scale0); hog.setNumLevels(nlevels)
+    got = hog.detectMultiScale(img, slot=slot)
+    kw = dict(win_stride=win_stride, scale0=scale0, nlevels=nlevels, g=g)
+    exp, _ = port.detect_multiscale(img, det, hit_threshold=hit, group_threshold=group, **kw)
+    if np.array_equal(got, exp):
+        return True, got, exp
+    lo, _ = port.detect_multiscale(img, det, hit_threshold=hit - SCORE_TOL, group_threshold=0, **kw)
+    hi, _ = port.detect_multiscale(img, det, hit_threshold=hit + SCORE_TOL, group_threshold=0, **kw)
+    hog.setGroupThreshold(0)
+    raw = hog.detectMultiScale(img, slot=slot)
+    hog.setGroupThreshold(group)
+    s_lo = set(map(tuple, lo)); s_hi = set(map(tuple, hi)); s_raw = set(map(tuple, raw))
+    ok = s_hi <= s_raw <= s_lo and len(s_lo - s_hi) > 0
+    regrouped = port.group_rectangles(raw, group) if group > 0 else raw
+    ok = ok and np.array_equal(regrouped, got)
+    return ok, got, exp
