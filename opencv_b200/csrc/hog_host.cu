@@ -204,7 +204,7 @@ void resize_table(int src, int dst, bool is_x, std::vector<ResizeCoef>& out)
             // second tap is ALWAYS the pixel right of the first one and the kernels need a single column pointer
             if (s >= src - 1 && src >= 2) { c.s0 = src - 2; c.s1 = src - 1; c.c0 = (c0 << 16) | c1; }
         }
-        else      { c.s0 = clip(s, 0, src); c.s1 = clip(s + 1, 0, src); c.c0 = c0 << 16; c.c1 = c1 << 16; }   // rows: :1821-1825
+        else      { c.s0 = clip(s, 0, src); c.s1 = clip(s + 1, 0, src); c.c0 = c0; c.c1 = c1; }   // rows: :1821-1825
         out.push_back(c);
     }
 }

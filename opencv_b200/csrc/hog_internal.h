@@ -50,7 +50,7 @@ struct LevelDesc {
 //   column entry: s0 = left source column, s1 = min(s0 + 1, W - 1) (its weight is 0 at the right edge),
 //                 c0 = a0 | a1 << 16  (11-bit fixed-point weights, resize.cpp:3647-3655), c1 unused
 //   row entry:    s0 / s1 = the two source rows AFTER the clip of resize.cpp:1821-1825,
-//                 c0 = b0 << 16, c1 = b1 << 16  (so that umulhi(c, t) == (b * t) >> 16)
+//                 c0 = b0, c1 = b1  (11-bit fixed-point weights; b * (S >> 4) fits 32 bits)
 struct __align__(16) ResizeCoef { int s0, s1; unsigned c0, c1; };
 
 // work item of the fused gradient+histogram kernel (one warp): a strip of block rows x a tile of block columns;

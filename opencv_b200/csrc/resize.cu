@@ -48,6 +48,10 @@ constexpr int kRsHeader = 16 + 16 * kRsMaxRows;             // mbarrier + per-ro
 constexpr int kRsWarpBytes = HOGB200_RS_BYTES;                        // staged source pixels per warp
 constexpr int kRsWarpStride = kRsHeader + kRsWarpBytes;
 constexpr int kRsDirectRows = 16;                           // rows per warp of the unstaged paths
+#ifndef HOGB200_RS_CHUNKS
+#define HOGB200_RS_CHUNKS 4
+#endif
+constexpr int kRsChunks = HOGB200_RS_CHUNKS;                // staged path: a warp walks down this many chunks of R rows, restaging its slice for each
 
 struct HRow { int t[4]; };        // horizontal result >> 4 of the four channels (resize.cpp:1596: S0[x] >> 4)
 
@@ -73,15 +77,17 @@ __device__ __forceinline__ HRow hrow_smem(unsigned addr, unsigned a01)
     asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(p1) : "r"(addr));       // weight 0 where sx + 1 is outside the row
     return hrow_px(p0, p1, a01);
 }
-// resize.cpp:1594-1601: uchar(( ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2) for four channels; b0/b1 come
-// pre-shifted by 16 so that umulhi is the truncating product.  All fields stay below 2^11, so channels c and c+2
-// share a register from the first addition on.
+// resize.cpp:1594-1601: uchar(( ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2) for four channels.  b0, b1 <= 2048
+// and S>>4 < 2^15, so every product fits 32 bits and its truncated term is the product's upper half: ONE byte
+// permute takes the upper halves of channels c and c+2 into the two 16-bit fields of a register (all fields stay
+// below 2^11), the two taps and the rounding constant are added field-parallel, and a last permute assembles the bytes.
+// The only integer multiplies are the eight products (the multiplier pipe is what bounds this kernel).
 __device__ __forceinline__ unsigned vertical_pack(const HRow& h0, const HRow& h1, unsigned b0, unsigned b1)
 {
-    const unsigned p02 = (__umulhi(b0, (unsigned)h0.t[2]) * 65536u + __umulhi(b0, (unsigned)h0.t[0])) +
-                         (__umulhi(b1, (unsigned)h1.t[2]) * 65536u + __umulhi(b1, (unsigned)h1.t[0])) + 0x00020002u;
-    const unsigned p13 = (__umulhi(b0, (unsigned)h0.t[3]) * 65536u + __umulhi(b0, (unsigned)h0.t[1])) +
-                         (__umulhi(b1, (unsigned)h1.t[3]) * 65536u + __umulhi(b1, (unsigned)h1.t[1])) + 0x00020002u;
+    const unsigned x0 = b0 * (unsigned)h0.t[0], x1 = b0 * (unsigned)h0.t[1], x2 = b0 * (unsigned)h0.t[2], x3 = b0 * (unsigned)h0.t[3];
+    const unsigned y0 = b1 * (unsigned)h1.t[0], y1 = b1 * (unsigned)h1.t[1], y2 = b1 * (unsigned)h1.t[2], y3 = b1 * (unsigned)h1.t[3];
+    const unsigned p02 = __byte_perm(x0, x2, 0x7632) + __byte_perm(y0, y2, 0x7632) + 0x00020002u;
+    const unsigned p13 = __byte_perm(x1, x3, 0x7632) + __byte_perm(y1, y3, 0x7632) + 0x00020002u;
     return __byte_perm(p02 >> 2, p13 >> 2, 0x6240);
 }
 
@@ -184,9 +190,10 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int w = L.w, h = L.h, rs = L.rs_rows;
     const int R = rs > 0 ? rs : (rs < 0 ? -rs : kRsDirectRows);
-    const int y0 = it.y0 + warp * R;
+    const int RW = rs != 0 ? R * kRsChunks : R;              // rows of this warp
+    const int y0 = it.y0 + warp * RW;
     if (y0 >= h) return;                                     // the whole warp
-    const int nrows = min(R, h - y0);
+    const int nrows = min(RW, h - y0);
     const int xa = it.x0 + lane, xb = xa + 32;
     const bool va = xa < w, vb = xb < w;
     const int dpitch = L.pitch;
@@ -228,28 +235,10 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     int span = (xt[min(it.x0 + kRsTileW, w) - 1].s0 + 2 - c_lo + 3) & ~3; // through the second tap of the last column
     span = min(span, ((bw + 3) & ~3) - c_lo);                              // rows are readable up to the next multiple of 4
     const unsigned rowbytes = 4u * span;
-    ResizeCoef cyl = yt[min(lane, nrows - 1)];
-    const int r_lo = __shfl_sync(0xffffffffu, cyl.s0, 0);
-    const int r_hi = __shfl_sync(0xffffffffu, cyl.s1, nrows - 1);
-    const int nstaged = rs > 0 ? r_hi - r_lo + 1 : 2 * nrows;
-    const unsigned off0 = rs > 0 ? (cyl.s0 - r_lo) * rowbytes : 2 * lane * rowbytes;
-    const unsigned off1 = rs > 0 ? (cyl.s1 - r_lo) * rowbytes : off0 + rowbytes;
-    if (lane < nrows)
-        asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(ycoef + 16 * lane), "r"(off0), "r"(off1), "r"(cyl.c0), "r"(cyl.c1) : "memory");
-    if (lane == 0) mbar_init(mbar, 1);
-    __syncwarp();
-    if (lane == 0) mbar_expect_tx(mbar, nstaged * rowbytes);
     const uint8_t* __restrict__ src0 = base + 4 * c_lo;
-    if (rs > 0) {
-        for (int j = lane; j < nstaged; j += 32) bulk_g2s(tile + j * rowbytes, src0 + (size_t)(r_lo + j) * bpitch, rowbytes, mbar);
-    } else if (lane < nrows) {
-        bulk_g2s(tile + off0, src0 + (size_t)cyl.s0 * bpitch, rowbytes, mbar);
-        bulk_g2s(tile + off1, src0 + (size_t)cyl.s1 * bpitch, rowbytes, mbar);
-    }
     const unsigned cola = tile + 4 * (cxa.s0 - c_lo), colb = tile + 4 * (cxb.s0 - c_lo);
     const unsigned a01a = cxa.c0, a01b = cxb.c0;
-    mbar_wait(mbar, 0);
-
+    if (lane == 0) mbar_init(mbar, 1);
     // Horizontal results of two source rows live in A and B (per column).  `r1` is the staged offset of the row that
     // served as the LOWER tap of the previous destination row; when the next row's upper tap is that row, only one
     // new source row is needed and the two buffers swap roles (par) instead of being copied.  The offsets are the
@@ -257,30 +246,52 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     HRow Aa, Ba, Ab, Bb;
 #pragma unroll
     for (int c = 0; c < 4; c++) Aa.t[c] = Ba.t[c] = Ab.t[c] = Bb.t[c] = 0;
-    unsigned r1 = 0xffffffffu;
-    bool par = false;           // false: lower tap of the previous row is in B; true: in A
-    for (int k = 0; k < nrows; k++, dst += dpitch) {
-        unsigned o0, o1, b0, b1;
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(o0), "=r"(o1), "=r"(b0), "=r"(b1) : "r"(ycoef + 16 * k));
-        unsigned outa, outb;
-        if (o0 == r1) {
-            if (par) {
+    for (int ch = 0, k0 = 0; k0 < nrows; ch++, k0 += R, yt += R) {
+        const int nr = min(R, nrows - k0);                  // destination rows of this chunk
+        const ResizeCoef cyl = yt[min(lane, nr - 1)];
+        const int r_lo = __shfl_sync(0xffffffffu, cyl.s0, 0);
+        const int r_hi = __shfl_sync(0xffffffffu, cyl.s1, nr - 1);
+        const int nstaged = rs > 0 ? r_hi - r_lo + 1 : 2 * nr;
+        const unsigned off0 = rs > 0 ? (cyl.s0 - r_lo) * rowbytes : 2 * lane * rowbytes;
+        const unsigned off1 = rs > 0 ? (cyl.s1 - r_lo) * rowbytes : off0 + rowbytes;
+        __syncwarp();                                       // every lane is done with the previous chunk's slice and row table
+        if (lane < nr)
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(ycoef + 16 * lane), "r"(off0), "r"(off1), "r"(cyl.c0), "r"(cyl.c1) : "memory");
+        if (lane == 0) mbar_expect_tx(mbar, nstaged * rowbytes);
+        __syncwarp();
+        if (rs > 0) {
+            for (int j = lane; j < nstaged; j += 32) bulk_g2s(tile + j * rowbytes, src0 + (size_t)(r_lo + j) * bpitch, rowbytes, mbar);
+        } else if (lane < nr) {
+            bulk_g2s(tile + off0, src0 + (size_t)cyl.s0 * bpitch, rowbytes, mbar);
+            bulk_g2s(tile + off1, src0 + (size_t)cyl.s1 * bpitch, rowbytes, mbar);
+        }
+        mbar_wait(mbar, ch & 1);
+
+        unsigned r1 = 0xffffffffu;
+        bool par = false;           // false: lower tap of the previous row is in B; true: in A
+        for (int k = 0; k < nr; k++, dst += dpitch) {
+            unsigned o0, o1, b0, b1;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(o0), "=r"(o1), "=r"(b0), "=r"(b1) : "r"(ycoef + 16 * k));
+            unsigned outa, outb;
+            if (o0 == r1) {
+                if (par) {
+                    Ba = hrow_smem(cola + o1, a01a); Bb = hrow_smem(colb + o1, a01b);
+                    outa = vertical_pack(Aa, Ba, b0, b1); outb = vertical_pack(Ab, Bb, b0, b1);
+                } else {
+                    Aa = hrow_smem(cola + o1, a01a); Ab = hrow_smem(colb + o1, a01b);
+                    outa = vertical_pack(Ba, Aa, b0, b1); outb = vertical_pack(Bb, Ab, b0, b1);
+                }
+                par = !par;
+            } else {
+                Aa = hrow_smem(cola + o0, a01a); Ab = hrow_smem(colb + o0, a01b);
                 Ba = hrow_smem(cola + o1, a01a); Bb = hrow_smem(colb + o1, a01b);
                 outa = vertical_pack(Aa, Ba, b0, b1); outb = vertical_pack(Ab, Bb, b0, b1);
-            } else {
-                Aa = hrow_smem(cola + o1, a01a); Ab = hrow_smem(colb + o1, a01b);
-                outa = vertical_pack(Ba, Aa, b0, b1); outb = vertical_pack(Bb, Ab, b0, b1);
+                par = false;
             }
-            par = !par;
-        } else {
-            Aa = hrow_smem(cola + o0, a01a); Ab = hrow_smem(colb + o0, a01b);
-            Ba = hrow_smem(cola + o1, a01a); Bb = hrow_smem(colb + o1, a01b);
-            outa = vertical_pack(Aa, Ba, b0, b1); outb = vertical_pack(Ab, Bb, b0, b1);
-            par = false;
+            r1 = o1;
+            if (va) *reinterpret_cast<unsigned*>(dst) = outa;
+            if (vb) *reinterpret_cast<unsigned*>(dst + 128) = outb;
         }
-        r1 = o1;
-        if (va) *reinterpret_cast<unsigned*>(dst) = outa;
-        if (vb) *reinterpret_cast<unsigned*>(dst + 128) = outb;
     }
 }
 
@@ -363,7 +374,7 @@ resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     } else {
         const ResizeCoef cy = ytab[L.ytab_off + y];
         const int sy0 = cy.s0, sy1 = cy.s1;
-        const int b0 = (int)(cy.c0 >> 16), b1 = (int)(cy.c1 >> 16);
+        const int b0 = (int)cy.c0, b1 = (int)cy.c1;
         const uint8_t* r0 = base + (size_t)sy0 * bpitch;
         const uint8_t* r1 = base + (size_t)sy1 * bpitch;
 #pragma unroll
@@ -432,7 +443,7 @@ int resize_tile_h(int cn, int rs_rows)
 {
     if (cn != 4) return 8;
     if (resize_direct()) return kRdWarps * kRdRows;
-    return kRsWarps * (rs_rows > 0 ? rs_rows : (rs_rows < 0 ? -rs_rows : kRsDirectRows));
+    return kRsWarps * (rs_rows > 0 ? rs_rows * kRsChunks : (rs_rows < 0 ? -rs_rows * kRsChunks : kRsDirectRows));
 }
 
 // Destination rows per warp for one 8UC4 level, from the level's own coefficient tables: the largest R whose
