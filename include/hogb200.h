@@ -152,6 +152,22 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
  * cell order (cellX*2 + cellY) inside a block as in hog.cu:202 */
 int hogb200_block_histograms(hogb200_t* h, const hogb200_image* img, float* out, size_t capacity_floats,
                              int* blocks_x, int* blocks_y);
+/* hogb200_block_histograms without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arithmetic and output layout as hogb200_block_histograms, but
+ *   - the kernel's scratch (work-queue counters, level descriptor, work-item list) lives in a file-scope
+ *     `static __device__` array of hogb200_noalloc_scratch_bytes() = 256 KiB that every GPU loading the library holds
+ *     until exit; the call makes no cudaMalloc / cudaFree / allocating library call;
+ *   - img must be a DEVICE image, CV_8UC1 or CV_8UC4, rows 4-byte / 16-byte aligned, pitch covering the width rounded
+ *     up to 4 pixels (nothing can be staged); d_out is a 16-byte aligned DEVICE buffer of capacity_floats floats;
+ *   - limit: at most 32 704 work items of 14 block columns x 4..16 block rows (any image up to about 8192 x 8192);
+ *     larger images are refused with HOGB200_CAPACITY and a message naming the limit;
+ *   - the work is QUEUED on the handle's stream and the call returns without synchronising;
+ *   - every call (of every handle on that GPU) shares the one scratch array, which a set-up kernel rewrites: calls
+ *     that overlap on the GPU (different streams / handles) race.  Serialise them on one stream. */
+size_t hogb200_noalloc_scratch_bytes(void);
+int hogb200_block_histograms_noalloc(hogb200_t* h, const hogb200_image* img, float* d_out, size_t capacity_floats,
+                                     int* blocks_x, int* blocks_y);
 /* compute_confidence_hists (hog.cpp:383-397): SVM score of every window of one image for detector `slot`,
  * wins_y x wins_x floats row-major */
 int hogb200_window_scores(hogb200_t* h, int slot, const hogb200_image* img, float* out, size_t capacity_floats,

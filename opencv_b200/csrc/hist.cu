@@ -31,6 +31,7 @@
 #include "hog_internal.h"
 
 #include <cstdlib>
+#include <cstring>
 
 namespace hogk {
 
@@ -565,6 +566,79 @@ void launch_hist(const FrameSet& fs, const LevelDesc* d_levels, const HistItem* 
         if (!done) done = cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)) == cudaSuccess;
         hist_kernel<1><<<grid, kThreads, sizeof(Smem), st>>>(fs, d_levels, d_items, nitems, d_queue, gamma, bw, l2hys, d_hist);
     }
+}
+
+// ---- allocation-free variant (no counterpart in the reference) -------
+// The fused kernel needs scratch in device memory: the two work-queue counters, the level descriptor and the work-item
+// list.  Callers that may not call cudaMalloc (CUDA graph capture, tight serving loops) get them from a file-scope
+// array instead: every GPU that loads the library holds these kNoAllocScratchBytes until exit.  Every call shares the
+// array and a set-up kernel rewrites it, so calls that overlap on the GPU race (see include/hogb200.h).
+constexpr size_t kNoAllocScratchBytes = 256 * 1024;
+constexpr int kNoAllocLevelOff = 256, kNoAllocItemsOff = 512;
+constexpr int kNoAllocMaxItems = (int)((kNoAllocScratchBytes - kNoAllocItemsOff) / sizeof(HistItem));     // 32 704
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+
+// writes the queue counters (zero), the LevelDesc of the single level and the (tile, strip) work items; device code
+// may name the array directly
+__global__ void noalloc_setup_kernel(int w, int h, int nbx, int nby, int ntx, int strip, int nitems)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        unsigned int* q = reinterpret_cast<unsigned int*>(g_noalloc_scratch);
+        q[0] = q[1] = q[2] = q[3] = 0u;
+        LevelDesc L;
+        L.img = nullptr; L.pitch = 0;                 // level 0 aliases the caller's frame (FrameSet::base)
+        L.w = w; L.h = h; L.nbx = nbx; L.nby = nby; L.nwx = 0; L.nwy = 0;
+        L.hist_off = 0; L.score_off = 0; L.xtab_off = 0; L.ytab_off = 0; L.mode = 0; L.rs_rows = 0;
+        *reinterpret_cast<LevelDesc*>(g_noalloc_scratch + kNoAllocLevelOff) = L;
+    }
+    if (i < nitems) {
+        const int s = i / ntx, t = i - s * ntx;       // full strips first, the partial last strip at the end of the queue
+        HistItem it;
+        it.level = 0; it.bx0 = (short)(t * kTileBlocks); it.by0 = (short)(s * strip);
+        it.nby = (short)min(strip, nby - s * strip);
+        reinterpret_cast<HistItem*>(g_noalloc_scratch + kNoAllocItemsOff)[i] = it;
+    }
+}
+
+}  // namespace
+
+size_t hist_noalloc_scratch_bytes() { return kNoAllocScratchBytes; }
+
+// 0 = queued; 1 = image too large for the static scratch; 2 = CUDA error (cudaGetLastError holds it)
+int launch_hist_noalloc(const uint8_t* d_img, int pitch, int w, int h, int cn, int gamma, const BlockWeights& bw, float l2hys,
+                        float* d_out, int num_sms, cudaStream_t st, long long* items_needed)
+{
+    const int nbx = w >= kBlock ? (w - kBlock) / kCell + 1 : 0, nby = h >= kBlock ? (h - kBlock) / kCell + 1 : 0;
+    if (nbx <= 0 || nby <= 0) return 0;
+    const int ntx = (nbx + kTileBlocks - 1) / kTileBlocks;
+    // strips of 4..16 block rows: about two work items per worker (a taller strip recomputes less, balances worse)
+    const long long workers = (long long)num_sms * kWarps;
+    int strip = (int)(((long long)nby * ntx + 2 * workers - 1) / (2 * workers));
+    strip = strip < 4 ? 4 : strip > 16 ? 16 : strip;
+    const long long nitems = (long long)ntx * ((nby + strip - 1) / strip);
+    if (items_needed) *items_needed = nitems;
+    if (nitems > kNoAllocMaxItems) return 1;
+    // The array's name is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, once
+    // per device, with that device current.
+    static unsigned char* scratch_of[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 2;
+    if (!scratch_of[dev]) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_noalloc_scratch) != cudaSuccess || !p) return 2;
+        scratch_of[dev] = static_cast<unsigned char*>(p);
+    }
+    unsigned char* scratch = scratch_of[dev];
+    noalloc_setup_kernel<<<(int)((nitems + 255) / 256), 256, 0, st>>>(w, h, nbx, nby, ntx, strip, (int)nitems);
+    FrameSet fs; memset(&fs, 0, sizeof fs);
+    fs.base[0] = d_img; fs.pitch[0] = pitch; fs.nframes = 1;
+    launch_hist(fs, reinterpret_cast<const LevelDesc*>(scratch + kNoAllocLevelOff),
+                reinterpret_cast<const HistItem*>(scratch + kNoAllocItemsOff), (int)nitems,
+                reinterpret_cast<unsigned int*>(scratch), num_sms, cn, gamma, bw, l2hys, d_out, st);
+    return cudaGetLastError() == cudaSuccess ? 0 : 2;
 }
 
 }  // namespace hogk

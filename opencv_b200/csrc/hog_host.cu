@@ -1309,6 +1309,42 @@ int hogb200_block_histograms(hogb200_t* h, const hogb200_image* img, float* out,
     return HOGB200_OK;
 }
 
+size_t hogb200_noalloc_scratch_bytes(void) { return hist_noalloc_scratch_bytes(); }
+
+int hogb200_block_histograms_noalloc(hogb200_t* h, const hogb200_image* img, float* d_out, size_t capacity_floats,
+                                     int* blocks_x, int* blocks_y)
+{
+    H_OR_FAIL;
+    int rc;
+    if ((rc = check_image(img))) return rc;
+    if (!img->on_device) return fail(HOGB200_BAD_ARG, "block_histograms_noalloc: the image must be in device memory (no staging buffer is allocated)");
+    const int cn = img->channels;
+    if (cn != 1 && cn != 4) return fail(HOGB200_BAD_ARG, "block_histograms_noalloc: CV_8UC1 or CV_8UC4 (widening 8UC3 needs a buffer)");
+    // the kernel reads rows in 4-pixel vectors straight from the caller's buffer: nothing can be staged here
+    const size_t al = cn == 4 ? 16 : 4, row = (size_t)img->width * cn;
+    if ((uintptr_t)img->data % al != 0 || img->pitch % al != 0 || img->pitch >= (1u << 30) ||
+        !(img->width % 4 == 0 || img->pitch >= align_up(row, al)))
+        return fail(HOGB200_BAD_ARG, "block_histograms_noalloc: rows must be 16-byte (8UC4) / 4-byte (8UC1) aligned, and the pitch must "
+                                     "cover the width rounded up to 4 pixels");
+    const int nbx = img->width >= kBlock ? (img->width - kBlock) / kCell + 1 : 0;
+    const int nby = img->height >= kBlock ? (img->height - kBlock) / kCell + 1 : 0;
+    if (blocks_x) *blocks_x = nbx;
+    if (blocks_y) *blocks_y = nby;
+    const size_t n = (size_t)nbx * nby * kHist;
+    if (n > capacity_floats) return fail(HOGB200_CAPACITY, "output capacity too small");
+    if (!n) return HOGB200_OK;
+    if (!d_out || (uintptr_t)d_out % 16 != 0) return fail(HOGB200_BAD_ARG, "output must be a 16-byte aligned device pointer");
+    if ((rc = use_device(h))) return rc;
+    long long need = 0;
+    const int st = launch_hist_noalloc((const uint8_t*)img->data, (int)img->pitch, img->width, img->height, cn, h->gamma, h->weights,
+                                       (float)h->l2hys, d_out, h->num_sms, h->stream, &need);
+    if (st == 1)
+        return fail(HOGB200_CAPACITY, "block_histograms_noalloc: image needs " + std::to_string(need) + " work items, the static scratch (" +
+                                      std::to_string(hist_noalloc_scratch_bytes()) + " bytes) holds 32704: use hogb200_block_histograms");
+    if (st) return fail(HOGB200_CUDA_ERROR, std::string("block_histograms_noalloc: ") + cudaGetErrorString(cudaGetLastError()));
+    return HOGB200_OK;
+}
+
 int hogb200_window_scores(hogb200_t* h, int slot, const hogb200_image* img, float* out, size_t capacity_floats,
                           int* wins_x, int* wins_y)
 {

@@ -86,6 +86,12 @@ void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
 void launch_hist(const FrameSet& fs, const LevelDesc* d_levels, const HistItem* d_items,
                  int nitems, unsigned int* d_queue, int num_sms, int cn, int gamma, const BlockWeights& bw,
                  float l2hys, float* d_hist, cudaStream_t st);
+// allocation-free variant: queue counters, level descriptor and work items live in a file-scope __device__ array of
+// hist.cu (hist_noalloc_scratch_bytes()); single image, output straight into the caller's device buffer.
+// 0 = queued, 1 = image needs more work items than the static scratch holds (*items_needed), 2 = CUDA error
+int launch_hist_noalloc(const uint8_t* d_img, int pitch, int w, int h, int cn, int gamma, const BlockWeights& bw, float l2hys,
+                        float* d_out, int num_sms, cudaStream_t st, long long* items_needed);
+size_t hist_noalloc_scratch_bytes();
 int hist_workers_per_sm();  // warps pulling items from the queue, per SM (the host balances the item list for them)
 
 struct SvmParams {

@@ -95,6 +95,9 @@ def load_library():
     L.hogb200_resize.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_int, C.c_int, C.c_void_p]
     L.hogb200_block_histograms.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_void_p, C.c_size_t,
                                            C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.hogb200_block_histograms_noalloc.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_void_p, C.c_size_t,
+                                                   C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.hogb200_noalloc_scratch_bytes.restype = C.c_size_t
     L.hogb200_window_scores.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Image), C.c_void_p, C.c_size_t,
                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.hogb200_group_rectangles.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
@@ -342,6 +345,14 @@ class HOG:
         self._ck(self._L.hogb200_block_histograms(self._h, C.byref(im), out.ctypes.data, out.size, C.byref(bx), C.byref(by)))
         assert (bx.value, by.value) == (out.shape[1], out.shape[0]) or out.size == 0
         return out
+
+    def blockHistogramsNoAlloc(self, img, out):
+        """hogb200_block_histograms_noalloc: `img` a CUDA uint8 tensor, `out` a CUDA float32 tensor (blocks_y, blocks_x, 36)
+        that receives the histograms; queued on the handle's stream, no allocation, no synchronisation."""
+        keep = []; im = _as_image(img, keep)
+        bx, by = C.c_int(), C.c_int()
+        self._ck(self._L.hogb200_block_histograms_noalloc(self._h, C.byref(im), out.data_ptr(), out.numel(), C.byref(bx), C.byref(by)))
+        return bx.value, by.value
 
     def windowScores(self, img, slot=0):
         keep = []; im = _as_image(img, keep)
