@@ -181,6 +181,13 @@ int hogb200_group_rectangles(hogb200_rect* rects, size_t n, int group_threshold,
 int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n, int group_threshold, double eps,
                                     size_t* count);
 
+/* cv::groupRectangles_meanshift(rectList, foundWeights, foundScales, detectThreshold, winDetSize)
+ * (objdetect/src/cascadedetect.cpp:176-395): the grouping cv::HOGDescriptor::detectMultiScale uses with
+ * useMeanshiftGrouping (objdetect/src/hog.cpp:2100-2101).  rects / weights (SVM scores) / scales (pyramid scale of each
+ * hit) have n entries; in place, *count modes survive (weights then hold the mode densities).  Host-only. */
+int hogb200_group_rectangles_meanshift(hogb200_rect* rects, double* weights, const double* scales, size_t n,
+                                       double detect_threshold, int win_w, int win_h, size_t* count);
+
 /* frames the batch entry point hands to one launch of each kernel for frames of this shape under the handle's current
  * scale factor / nlevels (instrumentation: bench.py quotes its roofline on launches of this size) */
 int hogb200_batch_group(const hogb200_t* h, int width, int height, int channels);

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhogb200.so")
-SOURCES = ["resize.cu", "hist.cu", "svm.cu", "group.cu", "hog_host.cu", "hog_storage.cu", "tbd_host.cpp"]
+SOURCES = ["resize.cu", "hist.cu", "svm.cu", "group.cu", "hog_host.cu", "hog_storage.cu", "tbd_host.cpp", "group_ms.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-O2,-ffp-contract=off", "--use_fast_math=false"]

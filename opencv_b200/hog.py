@@ -102,6 +102,8 @@ def load_library():
                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.hogb200_group_rectangles.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
     L.hogb200_group_rectangles_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
+    L.hogb200_group_rectangles_meanshift.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_int, C.c_int,
+                                                     C.POINTER(C.c_size_t)]
     L.hogb200_batch_group.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     L.hogb200_model_read.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_model_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t]
@@ -383,6 +385,21 @@ class HOG:
         if rc:
             raise HogError(rc, L.hogb200_last_error().decode())
         return r[:n.value].copy()
+
+    @staticmethod
+    def groupRectanglesMeanshift(rects, weights, scales, detect_threshold=0.0, win_size=(64, 128)):
+        """cv::groupRectangles_meanshift -> (rects (M,4) int32, weights (M,) float64).  Host only."""
+        L = load_library()
+        r = np.ascontiguousarray(np.asarray(rects, np.int32).reshape(-1, 4)).copy()
+        w = np.ascontiguousarray(np.asarray(weights, np.float64).reshape(-1)).copy()
+        sc = np.ascontiguousarray(np.asarray(scales, np.float64).reshape(-1))
+        assert len(r) == len(w) == len(sc)
+        n = C.c_size_t()
+        rc = L.hogb200_group_rectangles_meanshift(r.ctypes.data, w.ctypes.data, sc.ctypes.data, len(r), detect_threshold,
+                                                  win_size[0], win_size[1], C.byref(n))
+        if rc:
+            raise HogError(rc, "groupRectangles_meanshift: bad arguments")
+        return r[:n.value].copy(), w[:n.value].copy()
 
     def batchGroup(self, width, height, channels=4):
         """frames per kernel launch the batch path uses for this frame shape"""

@@ -181,6 +181,74 @@ long cvref_group_rectangles(int* rects, long n, int group_threshold, double eps)
     REF_CATCH
 }
 
+// cv::groupRectangles_meanshift(rectList, foundWeights, foundScales, detectThreshold, winDetSize)
+// (modules/objdetect/src/cascadedetect.cpp:387-394) -- the grouping HOGDescriptor::detectMultiScale uses with
+// useMeanshiftGrouping (objdetect/src/hog.cpp:2100-2101).  In place; returns the new count.
+long cvref_group_rectangles_meanshift(int* rects, double* weights, const double* scales, long n,
+                                      double detect_threshold, int win_w, int win_h)
+{
+    REF_TRY
+    std::vector<Rect> v((size_t)n); std::vector<double> w(weights, weights + n), sc(scales, scales + n);
+    for (long i = 0; i < n; i++) v[i] = Rect(rects[4*i], rects[4*i+1], rects[4*i+2], rects[4*i+3]);
+    groupRectangles_meanshift(v, w, sc, detect_threshold, Size(win_w, win_h));
+    for (size_t i = 0; i < v.size(); i++) {
+        rects[4*i] = v[i].x; rects[4*i+1] = v[i].y; rects[4*i+2] = v[i].width; rects[4*i+3] = v[i].height;
+        weights[i] = w[i];
+    }
+    return (long)v.size();
+    REF_CATCH
+}
+
+// HOGDescriptor::detectROI (modules/objdetect/src/hog.cpp:3549-3660): scores the requested window origins of ONE image.
+// confidences gets one entry per location (-10 for a location outside the padded image); returns the number of hits.
+long cvref_detect_roi(const int* geom, double win_sigma, double l2hys, int gamma, const float* svm, int nsvm,
+                      const unsigned char* img, int w, int h, int cn, long pitch,
+                      const int* locations, long nloc, double hit_threshold, int pad_w, int pad_h,
+                      int* found_xy, double* confidences)
+{
+    REF_TRY
+    HOGDescriptor hog = makeHog(geom, win_sigma, l2hys, gamma, 64);
+    hog.setSVMDetector(std::vector<float>(svm, svm + nsvm));
+    Mat m = toCpuHogInput(wrap(img, w, h, cn, pitch));
+    std::vector<Point> loc((size_t)nloc), found; std::vector<double> conf;
+    for (long i = 0; i < nloc; i++) loc[i] = Point(locations[2*i], locations[2*i+1]);
+    hog.detectROI(m, loc, found, conf, hit_threshold, Size(), Size(pad_w, pad_h));
+    for (size_t i = 0; i < conf.size(); i++) confidences[i] = conf[i];
+    for (size_t i = 0; i < found.size(); i++) { found_xy[2*i] = found[i].x; found_xy[2*i+1] = found[i].y; }
+    return (long)found.size();
+    REF_CATCH
+}
+
+// HOGDescriptor::detectMultiScaleROI (hog.cpp:3662-3677), unmodified (INTER_LINEAR_EXACT levels, padding 8x8,
+// groupRectangles(found, groupThreshold, 0.2)).  scales[nroi]; the locations of roi i are
+// locations[2*off[i] .. 2*off[i+1]); confidences (same indexing) receives every location's score.
+long cvref_detect_multiscale_roi(const int* geom, double win_sigma, double l2hys, int gamma, const float* svm, int nsvm,
+                                 const unsigned char* img, int w, int h, int cn, long pitch,
+                                 const double* scales, const long* off, long nroi, const int* locations,
+                                 double hit_threshold, int group_threshold,
+                                 int* rects, long capacity, double* confidences)
+{
+    REF_TRY
+    HOGDescriptor hog = makeHog(geom, win_sigma, l2hys, gamma, 64);
+    hog.setSVMDetector(std::vector<float>(svm, svm + nsvm));
+    Mat m = toCpuHogInput(wrap(img, w, h, cn, pitch));
+    std::vector<DetectionROI> rois((size_t)nroi);
+    for (long i = 0; i < nroi; i++) {
+        rois[i].scale = scales[i];
+        for (long j = off[i]; j < off[i + 1]; j++) rois[i].locations.push_back(Point(locations[2*j], locations[2*j+1]));
+    }
+    std::vector<Rect> found;
+    hog.detectMultiScaleROI(m, found, rois, hit_threshold, group_threshold);
+    for (long i = 0; i < nroi; i++)
+        for (size_t j = 0; j < rois[i].confidences.size(); j++) confidences[off[i] + j] = rois[i].confidences[j];
+    if ((long)found.size() > capacity) { g_err = "capacity"; return -1; }
+    for (size_t i = 0; i < found.size(); i++) {
+        rects[4*i] = found[i].x; rects[4*i+1] = found[i].y; rects[4*i+2] = found[i].width; rects[4*i+3] = found[i].height;
+    }
+    return (long)found.size();
+    REF_CATCH
+}
+
 // which: 0 = 64x128 INRIA default people detector (3781), 1 = 48x96 Daimler (1981)
 long cvref_people_detector(int which, float* out, long capacity)
 {

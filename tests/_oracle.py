@@ -251,6 +251,44 @@ class Ref:
         n = self._chk(self.L.cvref_group_rectangles(_vp(r), C.c_long(len(r)), thr, C.c_double(eps)))
         return r[:n].copy()
 
+    def group_rectangles_meanshift(self, rects, weights, scales, detect_threshold=0.0, win=(64, 128)):
+        """cv::groupRectangles_meanshift of the unmodified reference (cascadedetect.cpp:387-394)."""
+        r = np.ascontiguousarray(rects, np.int32).reshape(-1, 4).copy()
+        w = np.ascontiguousarray(weights, np.float64).copy(); sc = np.ascontiguousarray(scales, np.float64)
+        self.L.cvref_group_rectangles_meanshift.restype = C.c_long
+        n = self._chk(self.L.cvref_group_rectangles_meanshift(_vp(r), _vp(w), _vp(sc), C.c_long(len(r)),
+                                                              C.c_double(detect_threshold), win[0], win[1]))
+        return r[:n].copy(), w[:n].copy()
+
+    def detect_roi(self, img, svm, locations, hit_threshold=0.0, padding=(8, 8), g=DEFAULT_GEOM):
+        """HOGDescriptor::detectROI of the unmodified reference (objdetect/src/hog.cpp:3549-3660)
+        -> (found (M,2) int32, confidences (len(locations),) float64)."""
+        img, w, h, cn, pitch = _img(img)
+        svm = np.ascontiguousarray(svm, np.float32)
+        loc = np.ascontiguousarray(locations, np.int32).reshape(-1, 2)
+        found = np.zeros((max(len(loc), 1), 2), np.int32); conf = np.zeros(max(len(loc), 1), np.float64)
+        self.L.cvref_detect_roi.restype = C.c_long
+        n = self._chk(self.L.cvref_detect_roi(*self._g(g), _vp(svm), svm.size, _vp(img), w, h, cn, pitch, _vp(loc),
+                                              C.c_long(len(loc)), C.c_double(hit_threshold), padding[0], padding[1],
+                                              _vp(found), _vp(conf)))
+        return found[:n].copy(), conf[:len(loc)].copy()
+
+    def detect_multiscale_roi(self, img, svm, rois, hit_threshold=0.0, group_threshold=0, g=DEFAULT_GEOM, capacity=1 << 20):
+        """HOGDescriptor::detectMultiScaleROI, unmodified (hog.cpp:3662-3677).  rois: list of (scale, (K,2) locations)
+        -> (rects (M,4), [confidences per roi])."""
+        img, w, h, cn, pitch = _img(img)
+        svm = np.ascontiguousarray(svm, np.float32)
+        scales = np.array([r[0] for r in rois], np.float64)
+        locs = [np.asarray(r[1], np.int32).reshape(-1, 2) for r in rois]
+        off = np.zeros(len(rois) + 1, np.int64); off[1:] = np.cumsum([len(l) for l in locs])
+        allloc = np.ascontiguousarray(np.concatenate(locs) if locs else np.zeros((0, 2), np.int32))
+        rects = np.zeros((capacity, 4), np.int32); conf = np.zeros(max(int(off[-1]), 1), np.float64)
+        self.L.cvref_detect_multiscale_roi.restype = C.c_long
+        n = self._chk(self.L.cvref_detect_multiscale_roi(*self._g(g), _vp(svm), svm.size, _vp(img), w, h, cn, pitch, _vp(scales),
+                                                         _vp(off), C.c_long(len(rois)), _vp(allloc), C.c_double(hit_threshold),
+                                                         group_threshold, _vp(rects), C.c_long(capacity), _vp(conf)))
+        return rects[:n].copy(), [conf[off[i]:off[i + 1]].copy() for i in range(len(rois))]
+
 
 def synthetic_frame(seed, w, h, cn, blur=True, silhouettes=0):
     """Deterministic synthetic frame, numpy only (identical bytes on every machine).

@@ -100,3 +100,33 @@ def test_headers_are_plain_c(tmp_path):
     src = tmp_path / "abi.c"
     src.write_text('#include "hogb200.h"\n#include "tbdb200.h"\nint main(void) { hogb200_geom g; tbdb200_args a; (void)g; (void)a; return 0; }\n')
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), str(src)])
+
+
+def test_group_rectangles_meanshift_equals_reference():
+    """hogb200_group_rectangles_meanshift (host) against the unmodified cv::groupRectangles_meanshift: identical rects in
+    identical order, mode densities to 1e-9 relative -- clustered hits over several pyramid scales, isolated hits, ties,
+    a threshold that drops some modes, and the empty list."""
+    from _oracle import Ref
+    from opencv_b200 import HOG
+    if not Ref.available():
+        pytest.skip("oracle/_ref not present")
+    ref = Ref()
+    for seed in range(12):
+        rng = np.random.RandomState(seed)
+        n = int(rng.randint(1, 120))
+        k = rng.randint(0, 4, n)
+        lvl = rng.randint(0, 12, n)
+        sc = 1.05 ** lvl
+        cx = np.array([200, 520, 800, 330])[k] + rng.randint(-12, 13, n); cy = np.array([220, 300, 150, 400])[k] + rng.randint(-20, 21, n)
+        w = np.rint(64 * sc).astype(np.int32); h = np.rint(128 * sc).astype(np.int32)
+        rects = np.stack([cx - w // 2, cy - h // 2, w, h], 1).astype(np.int32)
+        wts = rng.uniform(0.05, 2.0, n)
+        if seed % 3 == 0:
+            rects[n // 2:] = rects[:n - n // 2]; wts[n // 2:] = wts[:n - n // 2]; sc[n // 2:] = sc[:n - n // 2]     # exact duplicates
+        for thr in (0.0, 0.02, 1.0):
+            er, ew = ref.group_rectangles_meanshift(rects, wts, sc, thr)
+            gr, gw = HOG.groupRectanglesMeanshift(rects, wts, sc, thr)
+            assert np.array_equal(gr, er), (seed, thr)
+            assert np.allclose(gw, ew, rtol=1e-9, atol=0)
+    gr, gw = HOG.groupRectanglesMeanshift(np.zeros((0, 4), np.int32), [], [])
+    assert len(gr) == 0 and len(gw) == 0

@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")/.."
 name=$1; shift
 mkdir -p build_variants/$name
-for f in resize.cu hist.cu svm.cu group.cu hog_host.cu hog_storage.cu tbd_host.cpp; do
+for f in resize.cu hist.cu svm.cu group.cu hog_host.cu hog_storage.cu tbd_host.cpp group_ms.cpp; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-O2 "$@" -c opencv_b200/csrc/$f -o build_variants/$name/${f%.*}.o &
 done
 wait
