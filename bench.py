@@ -313,27 +313,40 @@ def main():
     n_global = BATCH * world
     my_ids = shard_indices(n_global, rank, world)
 
-    def one_step(frames, gather, capacity):
-        out = hog.detectMultiScaleBatch(frames, nslots=NSLOTS, capacity=capacity)
+    def finish_step(out, gather):
         if NSLOTS > 1:                             # one list per frame: its detectors' boxes together
-            out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(frames))]
+            out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(out) // NSLOTS)]
         t = hog.lastTimings()
         if gather:                                 # boxes of all ranks -> rank 0, frame order, on the host (shard.py)
             merged = gather_detections(dict(zip(my_ids, out)), n_global, rank, world, group=host_group)
             assert merged is None or len(merged) == n_global
         return sum(len(o) for o in out), t["kernel_launches"], t["candidates"]
 
-    def timed(frames, steps, gather=False, capacity=1 << 20, seconds=None):
-        """K steps (or, with `seconds`, as many steps as fit) between two events on the launching stream."""
+    def timed(frames, steps, gather=False, capacity=1 << 20, seconds=None, pipelined=True):
+        """K steps (or, with `seconds`, as many steps as fit) between two events on the launching stream.  pipelined: the
+        asynchronous entry points with two batches in flight (submit k + 1, then collect k) -- the way a frame loop drives
+        the library; else the blocking call."""
         barrier()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         nrects = 0; launches = 0; cands = 0; done = 0
         t0 = time.perf_counter()
+        more = lambda: done < steps or (seconds is not None and time.perf_counter() - t0 < seconds)
         with torch.cuda.stream(stream):
             e0.record(stream)
-            while done < steps or (seconds is not None and time.perf_counter() - t0 < seconds):
-                a, b, c = one_step(frames, gather, capacity)
-                nrects += a; launches += b; cands += c; done += 1
+            if pipelined:
+                pending = hog.submitBatch(frames, nslots=NSLOTS)
+                while True:
+                    done += 1
+                    nxt = hog.submitBatch(frames, nslots=NSLOTS) if more() else None
+                    a, b, c = finish_step(hog.collectBatch(pending, capacity=capacity), gather)
+                    nrects += a; launches += b; cands += c
+                    if nxt is None:
+                        break
+                    pending = nxt
+            else:
+                while more():
+                    a, b, c = finish_step(hog.detectMultiScaleBatch(frames, nslots=NSLOTS, capacity=capacity), gather)
+                    nrects += a; launches += b; cands += c; done += 1
             e1.record(stream)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
@@ -355,13 +368,21 @@ def main():
     fps_e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
     h2d = BATCH * W * H * CN
     d2h = int(16 * ((BATCH + 63) // 64) + 16 * max(cands_e2e, 0) / max(args.steps, 1))
+    # the blocking entry point (one batch at a time, every call ends with a synchronisation), for comparison
+    timed(dev, 3, pipelined=False)
+    ms_b, _, _, _, _ = timed(dev, args.steps, pipelined=False)
+    timed(pinned_np, 3, gather=True, pipelined=False)
+    ms_be, _, _, _, _ = timed(pinned_np, args.steps, gather=True, pipelined=False)
 
     line = {"metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": CONFIG, "clocks": clocks,
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches, "detections_per_step": nrects / max(args.steps, 1)}
+            "gpu_launches": launches, "detections_per_step": nrects / max(args.steps, 1),
+            "api": "hogb200_submit_batch / hogb200_collect_batch, two batches in flight (value and e2e alike)",
+            "blocking_call": {"value": world * BATCH * args.steps / (ms_b * 1e-3), "e2e_value": world * BATCH * args.steps / (ms_be * 1e-3),
+                              "unit": UNIT, "api": "hogb200_detect_multiscale_batch"}}
 
     # ---- the same end-to-end measurement with detections: a hit threshold at which every frame yields thousands of
     # candidates (chosen from frame 0's own score distribution), so compaction under load, the candidate D2H, the
@@ -393,10 +414,12 @@ def main():
         hog.setSVMDetector(allpass)
         nb = min(8, BATCH)
         cap = nb * CONFIG["windows"] + 1024
-        timed(dev[:nb], 2, capacity=cap)
-        ms_p, nrects_p, _, cands_p, _ = timed(dev[:nb], 5, capacity=cap)
-        timed(pinned_np[:nb], 1, gather=True, capacity=cap)
-        ms_pe, _, _, _, _ = timed(pinned_np[:nb], 5, gather=True, capacity=cap)
+        # (blocking entry point: it sizes the candidate list to the worst case; the asynchronous one would overflow its
+        # 262 144-candidate region and re-run every chunk)
+        timed(dev[:nb], 2, capacity=cap, pipelined=False)
+        ms_p, nrects_p, _, cands_p, _ = timed(dev[:nb], 5, capacity=cap, pipelined=False)
+        timed(pinned_np[:nb], 1, gather=True, capacity=cap, pipelined=False)
+        ms_pe, _, _, _, _ = timed(pinned_np[:nb], 5, gather=True, capacity=cap, pipelined=False)
         line["pass_all_bias"] = {"value": world * nb * 5 / (ms_p * 1e-3), "e2e_value": world * nb * 5 / (ms_pe * 1e-3), "unit": UNIT,
                                  "frames_per_step_per_gpu": nb, "candidates_per_frame": cands_p / 5 / nb,
                                  "rects_per_frame": nrects_p / 5 / nb,

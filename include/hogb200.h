@@ -133,6 +133,16 @@ int hogb200_detect_multiscale_slot(hogb200_t* h, int slot, const hogb200_image* 
  * (offsets has nframes*nslots+1 entries). */
 int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, int nframes, int nslots,
                                     hogb200_rect* found, size_t capacity, size_t* offsets);
+/* The same batch, asynchronously -- the counterpart of the Stream& argument of HOG::compute (hog.cpp:490-534) for the
+ * detection path, whose reference form blocks on the null stream (hog.cpp:336-413): submit queues the uploads and kernels
+ * of the whole batch on the handle's streams and returns a ticket; collect waits for THAT batch, runs its tail (candidate
+ * ordering, rect scaling, groupRectangles -- on the device from HOGB200_GPU_POST_MIN = 1024 candidates per chunk) and
+ * fills found / offsets exactly as hogb200_detect_multiscale_batch does.  Two batches may be in flight per handle, so the
+ * uploads and kernels of batch k + 1 overlap the tail of batch k.  The frames' pixel buffers must stay valid, and the
+ * handle's parameters and detectors unchanged, until the batch is collected; no other work call of the handle may run
+ * in between.  Batches are collected in any order. */
+int hogb200_submit_batch(hogb200_t* h, const hogb200_image* frames, int nframes, int nslots, int* ticket);
+int hogb200_collect_batch(hogb200_t* h, int ticket, hogb200_rect* found, size_t capacity, size_t* offsets);
 /* compute (hog.cpp:490-534): descriptors of every window, wins x descriptor_size floats in
  * descriptor_format order.  out is a host pointer (out_on_device == 0) or a device pointer. */
 int hogb200_compute(hogb200_t* h, const hogb200_image* img, float* out, size_t capacity_floats,
@@ -187,6 +197,28 @@ int hogb200_group_rectangles_device(hogb200_t* h, hogb200_rect* rects, size_t n,
  * hit) have n entries; in place, *count modes survive (weights then hold the mode densities).  Host-only. */
 int hogb200_group_rectangles_meanshift(hogb200_rect* rects, double* weights, const double* scales, size_t n,
                                        double detect_threshold, int win_w, int win_h, size_t* count);
+
+/* ---- ROI variants: score only requested window origins, e.g. around tracker-predicted boxes.
+ * cv::HOGDescriptor::detectROI (objdetect/src/hog.cpp:3549-3660): `locations` are window origins in pixels of `img`
+ * (multiples of 8: the cache stride; the reference asserts the same in HOGCache::getBlock); windows may reach pad_w / pad_h
+ * pixels (rounded up to 8) outside the image, where gradients follow BORDER_REFLECT_101 as in the CPU class.
+ * confidences (nullable) receives one score per location, -10.0 for a location outside the padded image (:3596-3602);
+ * found / *count the locations with score >= hit threshold, in input order.  Detector slot 0. */
+int hogb200_detect_roi(hogb200_t* h, const hogb200_image* img, const hogb200_point* locations, size_t n, int pad_w, int pad_h,
+                       hogb200_point* found, double* confidences, size_t capacity, size_t* count);
+/* cv::DetectionROI (objdetect.hpp:345-353): one pyramid scale, the locations to evaluate IN THAT LEVEL's pixels, and (out,
+ * nullable) their confidences. */
+typedef struct hogb200_roi {
+    double scale;
+    const hogb200_point* locations;
+    size_t nlocations;
+    double* confidences;
+} hogb200_roi;
+/* cv::HOGDescriptor::detectMultiScaleROI (hog.cpp:3662-3677, worker :3489-3537): per roi the level cvRound(size / scale)
+ * (resized with the INTER_LINEAR pyramid semantics of this library), detectROI with padding 8 x 8, rects
+ * (cvRound(x*scale), cvRound(y*scale), cvRound(win*scale)) in roi order, then cv::groupRectangles(found, group_threshold, 0.2). */
+int hogb200_detect_multiscale_roi(hogb200_t* h, const hogb200_image* img, hogb200_roi* rois, size_t nrois, int group_threshold,
+                                  hogb200_rect* found, size_t capacity, size_t* count);
 
 /* frames the batch entry point hands to one launch of each kernel for frames of this shape under the handle's current
  * scale factor / nlevels (instrumentation: bench.py quotes its roofline on launches of this size) */

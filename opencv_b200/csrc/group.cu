@@ -226,4 +226,197 @@ int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int*
     return nout;
 }
 
+// =====================================================================================================================
+// Candidates of a whole chunk of frames -> rects, on the device (HOG_Impl::detectMultiScale's tail, cudaobjdetect/src/hog.cpp:
+// 471-487, for every (frame, detector) of the chunk at once): the compacted candidate list never travels to the host.
+//   1. sort by (segment = frame * ndet + detector, level, y, x): the reference's order (levels outermost, windows row-major);
+//   2. rect = (cvRound(x * stride * scale), cvRound(y * stride * scale), cvRound(win * scale)) in double, as hog.cpp:473-481;
+//   3. groupRectangles per segment with the kernels above: the x-sort key carries the segment in its upper half and the
+//      sweep stops at a segment boundary, so rects of different segments never unite; classes are numbered by a global scan
+//      over the root flags, which -- segments being contiguous in the sorted order -- numbers every segment's classes by
+//      first appearance, contiguously; the containment filter scans only the classes of its own segment.
+// No intermediate host synchronisation: kernels over classes are sized by n and read the class count from device memory.
+namespace {
+
+struct Cand { int level, x, y; float score; };      // = hogk::Candidate
+
+__global__ void cand_keys_kernel(const Cand* __restrict__ c, int n, int ndet, unsigned long long* __restrict__ keys, int* __restrict__ idx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Cand k = c[i];
+    const unsigned seg = (unsigned)(k.level >> 20) * ndet + ((k.level >> 16) & 15);
+    keys[i] = ((unsigned long long)seg << 40) | ((unsigned long long)(k.level & 0xffff) << 28) | ((unsigned long long)k.y << 14) | (unsigned)k.x;
+    idx[i] = i;
+}
+
+__global__ void cand_rects_kernel(const Cand* __restrict__ c, const unsigned long long* __restrict__ keys, const int* __restrict__ order,
+                                  int n, const __grid_constant__ CandGeom G, RectI* __restrict__ rects, int* __restrict__ seg,
+                                  unsigned long long* __restrict__ xkeys, int* __restrict__ idx, int* __restrict__ seg_count, int count_now)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Cand k = c[order[i]];
+    const double scale = G.scale[k.level & 0xffff];
+    RectI r;
+    r.x = __double2int_rn((double)(k.x * G.stride_x) * scale); r.y = __double2int_rn((double)(k.y * G.stride_y) * scale);
+    r.w = __double2int_rn(G.win_w * scale); r.h = __double2int_rn(G.win_h * scale);
+    rects[i] = r;
+    const int sg = (int)(keys[i] >> 40);
+    seg[i] = sg;
+    xkeys[i] = ((unsigned long long)sg << 32) | (unsigned)r.x;          // r.x >= 0: window origins are inside the level
+    idx[i] = i;
+    if (count_now) atomicAdd(&seg_count[sg], 1);                        // no grouping: every candidate is an output rect
+}
+
+__global__ void gather_seg_kernel(const RectI* __restrict__ r, const int* __restrict__ seg, const int* __restrict__ idx, int n,
+                                  RectI* __restrict__ sorted, int* __restrict__ sorted_seg, int* __restrict__ parent)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { sorted[i] = r[idx[i]]; sorted_seg[i] = seg[idx[i]]; parent[i] = i; }
+}
+
+__global__ void __launch_bounds__(256) unite_seg_kernel(const RectI* __restrict__ sorted, const int* __restrict__ sorted_seg,
+                                                        const int* __restrict__ idx, int n, double eps, int* __restrict__ parent)
+{
+    const int lane = threadIdx.x & 31;
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= n) return;
+    const RectI ra = sorted[a];
+    const int ia = idx[a], sa = sorted_seg[a];
+    const double reach = eps * (ra.w + ra.h) * 0.5;
+    for (int b = a + 1 + lane; ; b += 32) {
+        bool in_reach = false;
+        if (b < n) {
+            const RectI rb = sorted[b];
+            in_reach = sorted_seg[b] == sa && rb.x - ra.x <= reach;
+            if (in_reach && similar(ra, rb, eps)) uf_unite(parent, ia, idx[b]);
+        }
+        if (!__any_sync(0xffffffffu, in_reach)) break;
+    }
+}
+
+// sums = 5 ints per class; class -> segment, and every segment's class range [seg_lo, seg_hi]
+__global__ void accumulate_seg_kernel(const RectI* __restrict__ r, const int* __restrict__ seg, const int* __restrict__ root_of,
+                                      const int* __restrict__ class_of_root, int n, int* __restrict__ sums, int* __restrict__ class_seg,
+                                      int* __restrict__ seg_lo, int* __restrict__ seg_hi)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cls = class_of_root[root_of[i]];
+    int* s = sums + 5 * cls;
+    atomicAdd(s + 0, r[i].x); atomicAdd(s + 1, r[i].y); atomicAdd(s + 2, r[i].w); atomicAdd(s + 3, r[i].h);
+    atomicAdd(s + 4, 1);
+    if (root_of[i] == i) {
+        class_seg[cls] = seg[i];
+        atomicMin(&seg_lo[seg[i]], cls); atomicMax(&seg_hi[seg[i]], cls);
+    }
+}
+
+__global__ void filter_seg_kernel(const int* __restrict__ sums, const int* __restrict__ nclasses_p, const int* __restrict__ class_seg,
+                                  const int* __restrict__ seg_lo, const int* __restrict__ seg_hi, int thr, double eps,
+                                  int* __restrict__ keep, RectI* __restrict__ mean, int* __restrict__ seg_count, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i >= *nclasses_p) { keep[i] = 0; return; }
+    const int n1 = sums[5 * i + 4];
+    const RectI r1 = class_mean(sums + 5 * i);
+    mean[i] = r1;
+    const int sg = class_seg[i];
+    int k = n1 > thr;
+    for (int j = seg_lo[sg]; k && j <= seg_hi[sg]; j++) {
+        const int n2 = sums[5 * j + 4];
+        if (j == i || n2 <= thr) continue;
+        const RectI r2 = class_mean(sums + 5 * j);
+        const int dx = __double2int_rn(r2.w * eps), dy = __double2int_rn(r2.h * eps);
+        if (r1.x >= r2.x - dx && r1.y >= r2.y - dy && r1.x + r1.w <= r2.x + r2.w + dx && r1.y + r1.h <= r2.y + r2.h + dy &&
+            (n2 > max(3, n1) || n1 < 3))
+            k = 0;
+    }
+    keep[i] = k;
+    if (k) atomicAdd(&seg_count[sg], 1);
+}
+
+__global__ void emit_seg_kernel(const RectI* __restrict__ mean, const int* __restrict__ keep, const int* __restrict__ pos, int n,
+                                RectI* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && keep[i]) out[pos[i]] = mean[i];
+}
+
+__global__ void fill_kernel(int* __restrict__ p, int n, int v)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+size_t sort64_bytes(int n)
+{
+    size_t b = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, b, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (const int*)nullptr,
+                                    (int*)nullptr, n);
+    return b;
+}
+
+}  // namespace
+
+size_t cand_group_workspace_bytes(int n, int nseg)
+{
+    return 4 * align256((size_t)16 * n) + 2 * align256((size_t)8 * n) + 12 * align256((size_t)4 * n) + align256((size_t)20 * n) +
+           align256(sort64_bytes(n)) + 4 * align256((size_t)4 * nseg) + 1024;
+}
+
+// d_cand: n candidates of the chunk in device memory (any order).  On return *d_out_p points at the output rects in the
+// workspace (segment-major, reference order inside a segment) and *d_hdr_p at [total, count of segment 0, 1, ...] (ints),
+// both valid once `st` has drained.  Nothing is synchronised here.  Returns 0, or -1 on a CUDA error.
+int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandGeom& G, int thr, double eps, void* ws,
+                      cudaStream_t st, const int** d_out_p, const int** d_hdr_p)
+{
+    unsigned char* p = (unsigned char*)ws;
+    auto take = [&](size_t bytes) { void* r = p; p += align256(bytes); return r; };
+    RectI* d_rects = (RectI*)take((size_t)16 * n); RectI* d_sorted = (RectI*)take((size_t)16 * n);
+    RectI* d_mean = (RectI*)take((size_t)16 * n); RectI* d_out = (RectI*)take((size_t)16 * n);
+    unsigned long long* d_k1 = (unsigned long long*)take((size_t)8 * n); unsigned long long* d_k2 = (unsigned long long*)take((size_t)8 * n);
+    int* d_idx = (int*)take((size_t)4 * n); int* d_idx2 = (int*)take((size_t)4 * n);
+    int* d_seg = (int*)take((size_t)4 * n); int* d_sseg = (int*)take((size_t)4 * n);
+    int* d_parent = (int*)take((size_t)4 * n); int* d_root = (int*)take((size_t)4 * n);
+    int* d_flag = (int*)take((size_t)4 * n); int* d_scan = (int*)take((size_t)4 * n);
+    int* d_keep = (int*)take((size_t)4 * n); int* d_pos = (int*)take((size_t)4 * n);
+    int* d_cseg = (int*)take((size_t)4 * n); int* d_order = (int*)take((size_t)4 * n);
+    int* d_sums = (int*)take((size_t)20 * n);
+    size_t sort_bytes = sort64_bytes(n);
+    void* d_sort = take(sort_bytes);
+    int* d_hdr = (int*)take((size_t)4 * (nseg + 1));       // [total][count per segment]
+    int* d_lo = (int*)take((size_t)4 * nseg); int* d_hi = (int*)take((size_t)4 * nseg);
+    int* d_cnt = (int*)take(256);
+    const Cand* c = (const Cand*)d_cand;
+    const int T = 256, B = (n + T - 1) / T, BS = (nseg + T - 1) / T;
+
+    cudaMemsetAsync(d_hdr, 0, (size_t)4 * (nseg + 1), st);
+    cand_keys_kernel<<<B, T, 0, st>>>(c, n, ndet, d_k1, d_idx);
+    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_order, n, 0, 52, st);
+    cand_rects_kernel<<<B, T, 0, st>>>(c, d_k2, d_order, n, G, d_rects, d_seg, d_k1, d_idx, d_hdr + 1, thr <= 0);
+    *d_hdr_p = d_hdr;
+    if (thr <= 0) {             // cv::groupRectangles returns the list untouched (cascadedetect.cpp:66-75)
+        fill_kernel<<<1, 32, 0, st>>>(d_hdr, 1, n);
+        *d_out_p = &d_rects[0].x;
+        return cudaGetLastError() == cudaSuccess ? 0 : -1;
+    }
+    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_idx2, n, 0, 44, st);
+    gather_seg_kernel<<<B, T, 0, st>>>(d_rects, d_seg, d_idx2, n, d_sorted, d_sseg, d_parent);
+    unite_seg_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_sseg, d_idx2, n, eps, d_parent);
+    root_flags_kernel<<<B, T, 0, st>>>(d_parent, n, d_root, d_flag);
+    scan_kernel<<<1, 1024, 0, st>>>(d_flag, d_scan, n, d_cnt);            // d_cnt[0] = number of classes
+    cudaMemsetAsync(d_sums, 0, (size_t)20 * n, st);
+    fill_kernel<<<BS, T, 0, st>>>(d_lo, nseg, 0x7fffffff);
+    fill_kernel<<<BS, T, 0, st>>>(d_hi, nseg, -1);
+    accumulate_seg_kernel<<<B, T, 0, st>>>(d_rects, d_seg, d_root, d_scan, n, d_sums, d_cseg, d_lo, d_hi);
+    filter_seg_kernel<<<B, T, 0, st>>>(d_sums, d_cnt, d_cseg, d_lo, d_hi, thr, eps, d_keep, d_mean, d_hdr + 1, n);
+    scan_kernel<<<1, 1024, 0, st>>>(d_keep, d_pos, n, d_hdr);              // d_hdr[0] = number of output rects
+    emit_seg_kernel<<<B, T, 0, st>>>(d_mean, d_keep, d_pos, n, d_out);
+    *d_out_p = &d_out[0].x;
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 }  // namespace hogk

@@ -41,31 +41,38 @@ namespace {
 #define HOGB200_HIST_WARPS 12
 #endif
 #ifndef HOGB200_LUT_COPIES
-#define HOGB200_LUT_COPIES 16
+#define HOGB200_LUT_COPIES 32
 #endif
 constexpr int kWarps = HOGB200_HIST_WARPS;         // independent workers per CTA (one CTA per SM)
 constexpr int kThreads = kWarps * 32;
 constexpr int kTileCells = 15;                     // 30 voting lanes x 4 columns = 120 columns
 constexpr int kTileBlocks = kTileCells - 1;        // 14 blocks per tile row
-constexpr int kLutCopies = HOGB200_LUT_COPIES;     // gamma LUT replication (bank spreading)
+constexpr int kLutCopies = HOGB200_LUT_COPIES;     // gamma LUT replication (bank spreading; 32 = one copy per lane)
 constexpr int kPF = 4;                             // rows of load prefetch
 
+constexpr int kVote = 32;                          // elements per accumulator row and column class: lanes 1..30 vote into 0..29, the
+                                                   // halo lanes 0 / 31 into 31 / 30, which nobody reads.  The row stride must stay a
+                                                   // multiple of 128 B: lanes vote into DIFFERENT rows (bins) at once, and only then is
+                                                   // the bank a function of the lane alone (a 30-element row was tried: +47 % time)
 constexpr int kRows = kBins + 1;                   // accumulator rows per slot: row 9 aliases row 0 (second vote of row 8)
-constexpr int kBinBytes = 4 * 32 * 4;              // one accumulator row: [j][idx] float = 512 B
+constexpr int kColBytes = kVote * 4;               // one column class j of an accumulator row: [idx] float = 128 B
+constexpr int kBinBytes = 4 * kColBytes;           // one accumulator row: [j][idx] float = 512 B
 constexpr int kSlotBytes = kRows * kBinBytes;      // 5120 B
+constexpr int kStgBytes = kTileBlocks * kHist * 4; // 2016 B: the normalisation plane, aliased onto a slot that was just consumed
 constexpr float kMagic = 8388624.f;                // 2^23 + 16: q + kMagic has ulp 1 for q in [-4.5, 4.5], mantissa = 16 + n
+static_assert(kStgBytes <= kSlotBytes && kStgBytes % 16 == 0 && kSlotBytes % 16 == 0, "staging plane must fit a slot");
 
 struct __align__(16) WarpSmem {
-    float acc[3][kRows][4][32];                    // 15,360 B  vertical partial sums
-    float stg[kTileBlocks * kHist];                //  2,016 B  horizontal results of one block row
+    float acc[3][kRows][4][kVote];                 // 15,360 B  vertical partial sums
 };
 struct __align__(16) Smem {
     float4 wrow[3][8];                             //    384 B  vertical weights of row o of a cell row, per slot, for the
                                                    //           three role rotations (slot roles rotate, slots stay put)
     float4 wh[6];                                  //     96 B  horizontal weights, paired like the accumulator loads
-    float lut[256 * kLutCopies];                   // 16,384 B  gamma LUT, lut[v*copies + lane%copies]
-    WarpSmem w[kWarps];                            // 12 x 17,376 B
+    float lut[256 * kLutCopies];                   // 32,768 B  gamma LUT, lut[v*copies + lane%copies]: one copy per lane, no conflicts
+    WarpSmem w[kWarps];                            // 12 x 15,360 B
 };
+static_assert(sizeof(Smem) <= 227 * 1024, "shared memory");
 
 // ---- shared-memory access to the accumulators: 32-bit shared addresses, volatile so that the batches below
 // keep their order (loads first, then stores) and ptxas is free to overlap the latencies.
@@ -75,21 +82,21 @@ __device__ __forceinline__ float2 lds64(unsigned a)
     asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
     return v;
 }
-// one vote = two adjacent accumulator rows (bin0 and bin0 + 1), 512 B apart
+// one vote = two adjacent accumulator rows (bin0 and bin0 + 1), kBinBytes apart
 // OFF = byte offset of the slot: the three slots sit at fixed immediates from one address register
 template <int OFF>
 __device__ __forceinline__ float2 lds32x2(unsigned a)
 {
     float2 v;
     asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v.x) : "r"(a), "n"(OFF));
-    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v.y) : "r"(a), "n"(OFF + 512));
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v.y) : "r"(a), "n"(OFF + kBinBytes));
     return v;
 }
 template <int OFF>
 __device__ __forceinline__ void sts32x2(unsigned a, float2 v)
 {
     asm volatile("st.shared.f32 [%0+%1], %2;" ::"r"(a), "n"(OFF), "f"(v.x));
-    asm volatile("st.shared.f32 [%0+%1], %2;" ::"r"(a), "n"(OFF + 512), "f"(v.y));
+    asm volatile("st.shared.f32 [%0+%1], %2;" ::"r"(a), "n"(OFF + kBinBytes), "f"(v.y));
 }
 __device__ __forceinline__ void sts64_zero(unsigned a)
 {
@@ -244,11 +251,16 @@ __device__ __forceinline__ Vote pixel(const float (&L)[3], const float (&R)[3], 
     return v;
 }
 
-// Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row) into the staging plane;
-// also zeroes the accumulator for its next use.  lane <-> (accumulator row, cell): 2 rows x 15 cells per pass.
-__device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws, int cy, const float4* __restrict__ wh, int lane)
+// Horizontal contraction of one finished vertical accumulator (cell row `cy` of a block row); also zeroes the
+// accumulator for its next use.  lane <-> (accumulator row, cell): 2 rows x 15 cells per pass, 5 passes.  The results stay
+// in registers: ax[it] = (block `cell`, cx 0), bx[it] = (block `cell` - 1, cx 1), bin of accumulator row 2 it + half.
+__device__ __forceinline__ void horizontal_pass(unsigned slot_addr, const float4* __restrict__ wh, int lane, float (&ax)[5], float (&bx)[5])
 {
     const int cell = lane & 15, half = lane >> 4;
+    // the sixteenth lane of each half has no cell: it reads (and clears) the two elements the halo lanes vote into;
+    // whatever they hold only reaches sums nobody stores
+    const bool real = true;
+    const int ce = cell;
     // weights paired like the loads below: (column j, column 4 + j) of the cell
     // (registers, loaded from shared memory: FFMA2 takes no constant-bank operand)
     float2 w00[4], w11[4], wx[4];
@@ -263,22 +275,21 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
     for (int it = 0; it < 5; it++) {
         const int row = it * 2 + half;
         const bool act = row < kBins;        // row 9 only exists as the alias of row 0, folded in below
-        // lanes of cell 15 read (and clear) the two halo elements: whatever they hold only reaches sums nobody stores
-        const unsigned base = slot_addr + row * kBinBytes + cell * 8;
+        const unsigned base = slot_addr + (act ? row : 0) * kBinBytes + ce * 8;
         float2 v[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = lds64(base + j * 128);  // columns j and 4+j of the cell
+        for (int j = 0; j < 4; j++) v[j] = lds64(base + j * kColBytes);  // columns j and 4+j of the cell
         if (it == 0 && half == 0) {          // row 0 += row 9 (second votes of row 8: both are the same bin)
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const float2 t = lds64(base + 9 * kBinBytes + j * 128);
+                const float2 t = lds64(base + 9 * kBinBytes + j * kColBytes);
                 v[j].x += t.x; v[j].y += t.y;
-                sts64_zero(base + 9 * kBinBytes + j * 128);
+                if (real) sts64_zero(base + 9 * kBinBytes + j * kColBytes);
             }
         }
-        if (act) {
+        if (act && real) {
 #pragma unroll
-            for (int j = 0; j < 4; j++) sts64_zero(base + j * 128);
+            for (int j = 0; j < 4; j++) sts64_zero(base + j * kColBytes);
         }
         float2 p00 = make_float2(0.f, 0.f), p11 = p00, px = p00;
 #pragma unroll
@@ -289,23 +300,43 @@ __device__ __forceinline__ void horizontal_pass(unsigned slot_addr, WarpSmem& ws
         }
         const float s00 = p00.x + p00.y, s11 = p11.x + p11.y, s01 = px.x, s10 = px.y;
         // block k, cx=0 = own s00 + s01 of cell k+1 ; block k-1, cx=1 = own s11 + s10 of cell k-1
-        const float ax = s00 + __shfl_down_sync(0xffffffffu, s01, 1);
-        const float bx = s11 + __shfl_up_sync(0xffffffffu, s10, 1);
-        const int tb = row + 4 >= kBins ? row + 4 - kBins : row + 4;     // bin of this accumulator row
-        if (act && cell < kTileBlocks) ws.stg[cell * kHist + (0 * 2 + cy) * kBins + tb] = ax;
-        if (act && cell >= 1 && cell < kTileCells) ws.stg[(cell - 1) * kHist + (1 * 2 + cy) * kBins + tb] = bx;
+        ax[it] = s00 + __shfl_down_sync(0xffffffffu, s01, 1);
+        bx[it] = s11 + __shfl_up_sync(0xffffffffu, s10, 1);
     }
 }
 
-__device__ __forceinline__ void zero_slot(unsigned slot_addr, int lane)
+// results of the two horizontal passes of a block row -> the staging plane [block][cx*2+cy][bin]
+__device__ __forceinline__ void stage_results(unsigned stg, int lane, int cy, const float (&ax)[5], const float (&bx)[5])
 {
+    const int cell = lane & 15, half = lane >> 4;
 #pragma unroll
-    for (int i = 0; i < kSlotBytes / (32 * 16); i++) sts128_zero(slot_addr + (i * 32 + lane) * 16);
+    for (int it = 0; it < 5; it++) {
+        const int row = it * 2 + half;
+        if (row >= kBins) continue;
+        const int tb = row + 4 >= kBins ? row + 4 - kBins : row + 4;     // bin of this accumulator row
+        if (cell < kTileBlocks)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + 4 * (cell * kHist + (0 * 2 + cy) * kBins + tb)), "f"(ax[it]));
+        if (cell >= 1 && cell < kTileCells)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + 4 * ((cell - 1) * kHist + (1 * 2 + cy) * kBins + tb)), "f"(bx[it]));
+    }
+}
+
+__device__ __forceinline__ void zero_bytes(unsigned addr, int bytes, int lane)      // bytes: a multiple of 16
+{
+    for (int i = lane * 16; i < bytes; i += 32 * 16) sts128_zero(addr + i);
+}
+__device__ __forceinline__ void zero_slot(unsigned slot_addr, int lane) { zero_bytes(slot_addr, kSlotBytes, lane); }
+
+__device__ __forceinline__ float lds32(unsigned a)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
 }
 
 // L2-Hys (hog.cpp:1119-1248 / hog.cu:333-349) of the staged block row and coalesced store; 4 lanes per block,
-// one cell (9 bins) per lane.
-__device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk, float thr, float* __restrict__ out_row)
+// one cell (9 bins) per lane.  The plane sits in a slot that was just consumed: it is zeroed again on the way out.
+__device__ __forceinline__ void normalize_store(unsigned stg, int lane, int nblk, float thr, float* __restrict__ out_row)
 {
 #pragma unroll 1
     for (int g = 0; g < 2; g++) {
@@ -316,7 +347,7 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         float ss = 0.f;
 #pragma unroll
         for (int b = 0; b < kBins; b++) {
-            v[b] = ws.stg[idx + b];
+            v[b] = lds32(stg + 4 * (idx + b));
             ss = fmaf(v[b], v[b], ss);
         }
         ss += __shfl_xor_sync(0xffffffffu, ss, 1);
@@ -334,13 +365,17 @@ __device__ __forceinline__ void normalize_store(WarpSmem& ws, int lane, int nblk
         __syncwarp();       // every lane has read its inputs before any lane overwrites the plane
         if (live) {
 #pragma unroll
-            for (int b = 0; b < kBins; b++) ws.stg[idx + b] = v[b] * sc2;
+            for (int b = 0; b < kBins; b++) asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + 4 * (idx + b)), "f"(v[b] * sc2));
         }
     }
     __syncwarp();
-    const float4* src = reinterpret_cast<const float4*>(ws.stg);
     float4* dst = reinterpret_cast<float4*>(out_row);
-    for (int i = lane; i < nblk * (kHist / 4); i += 32) dst[i] = src[i];
+    for (int i = lane; i < kTileBlocks * (kHist / 4); i += 32) {
+        float4 t;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(stg + 16 * i));
+        sts128_zero(stg + 16 * i);           // the slot goes back to its accumulator role
+        if (i < nblk * (kHist / 4)) dst[i] = t;
+    }
 }
 
 template <int CN>
@@ -372,18 +407,23 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
     // accumulator slots: roles P (block row above, cell row 0), Q (above, cell row 1), R (this, cell row 0);
     // lane l votes into element (l-1)&31 of every [bin][j] row, rows of one slot are 1024 B apart
     const unsigned acc0 = (unsigned)__cvta_generic_to_shared(&ws.acc[0][0][0][0]);
-    // row index = n + 4, the mantissa of r holds n + 16 (the exponent bits leave through the `<< 9`)
-    const unsigned lane_off = ((lane - 1) & 31) * 4 + (4 - 16) * kBinBytes;
+    // row index = n + 4; r's bit pattern is 0x4B000000 + 16 + n, and bits * kBinBytes (mod 2^32) is the row offset plus a
+    // constant that is folded into the column base: one IMAD per pixel.  The halo lanes 0 / 31 vote into elements 31 / 30.
+    const int vidx = (lane - 1) & 31;
+    const unsigned lane_off = vidx * 4 + (4 - 16) * kBinBytes - 0x4B000000u * (unsigned)kBinBytes;
     // The slots stay at fixed offsets 0, 1, 2 x kSlotBytes from one address register (immediates in the inner loop);
     // what rotates after every cell row is which role a slot plays, i.e. which weight column it is fed with:
     // rot = 0: (P,Q,R) = slots (0,1,2); 1: (2,0,1); 2: (1,2,0).
     unsigned colbase[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) colbase[j] = acc0 + lane_off + j * 128;
+    for (int j = 0; j < 4; j++) colbase[j] = acc0 + lane_off + j * kColBytes;
     int rot = 0, slot_p = 0;
     zero_slot(acc0 + 2 * kSlotBytes, lane);                 // R; P and Q are cleared during the first cell row
     __syncwarp();
 
+    float pax[5], pbx[5];                                   // horizontal results of cell row 0 of the block row in flight
+#pragma unroll
+    for (int i = 0; i < 5; i++) pax[i] = pbx[i] = 0.f;
     int y = it.by0 * kCell;
     float U[4][3], C[4][3], D[4][3];
     typename RawT<CN>::T pf[kPF];
@@ -437,7 +477,7 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
                 unsigned ad[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    ad[j] = (v[j].rbits << 9) + colbase[j];
+                    ad[j] = v[j].rbits * (unsigned)kBinBytes + colbase[j];
                     a0[j] = lds32x2<0>(ad[j]); a1[j] = lds32x2<kSlotBytes>(ad[j]); a2[j] = lds32x2<2 * kSlotBytes>(ad[j]);
                 }
 #pragma unroll
@@ -459,13 +499,18 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
             const int ds = slot_p + hf >= 3 ? slot_p + hf - 3 : slot_p + hf;
             const unsigned done = acc0 + ds * kSlotBytes;
             if (cr == 0) zero_slot(done, lane);
-            else horizontal_pass(done, ws, hf, s.wh, lane);
-            __syncwarp();
-            if (hf && cr > 0) {
-                const int by = it.by0 + cr - 1;
-                normalize_store(ws, lane, nblk, l2hys, hist + L.hist_off + ((long long)by * L.nbx + it.bx0) * kHist);
+            else if (hf == 0) horizontal_pass(done, s.wh, lane, pax, pbx);     // cell row 0 of the block row: kept in registers
+            else {
+                float qax[5], qbx[5];
+                horizontal_pass(done, s.wh, lane, qax, qbx);
+                __syncwarp();                                                   // the slot is read out and zeroed: stage in it
+                stage_results(done, lane, 0, pax, pbx);
+                stage_results(done, lane, 1, qax, qbx);
                 __syncwarp();
+                const int by = it.by0 + cr - 1;
+                normalize_store(done, lane, nblk, l2hys, hist + L.hist_off + ((long long)by * L.nbx + it.bx0) * kHist);
             }
+            __syncwarp();
         }
         // rotate roles: R -> P, T (in P's slot) -> Q, Q's slot (just consumed and zeroed) -> R
         rot = rot == 2 ? 0 : rot + 1;

@@ -95,6 +95,30 @@ struct Plan {
     bool valid = false;
 };
 
+// One chunk (consecutive frames of one shape, at most 64) of an asynchronous batch: where its candidates go and what the
+// tail needs once the kernels are done.
+struct ChunkJob {
+    int f0 = 0, nf = 0;
+    size_t cand_off = 0, cap = 0;           // region of the job's candidate buffer: [16-byte header][Candidate * cap]
+    std::vector<LevelHost> lv;              // level scales of the plan the chunk ran on
+    long long nwindows = 0;
+    cudaEvent_t done = nullptr;             // kernels finished and the candidate count is in h_counts[4 * chunk]
+};
+// A batch in flight (hogb200_submit_batch .. hogb200_collect_batch).
+struct BatchJob {
+    bool active = false;
+    std::vector<hogb200_image> frames;      // the caller's descriptors (the pixel buffers stay the caller's)
+    int nslots = 0;
+    double hit_threshold = 0; int group_threshold = 0, stride_x = 0, stride_y = 0;     // parameters at submit time
+    std::vector<ChunkJob> chunks;
+    DevBuf<unsigned char> d_cand;
+    PinBuf<unsigned int> h_counts;
+    std::vector<cudaEvent_t> events;        // pool, reused from batch to batch
+    int launches = 0;
+    bool finished = false;                  // the tail has run; results wait for a collect call with enough capacity
+    std::vector<hogb200_rect> result; std::vector<size_t> result_off;
+};
+
 }  // namespace
 
 namespace hogk { int storage_fail(int code, const std::string& msg) { return fail(code, msg); } }
@@ -122,6 +146,12 @@ struct hogb200 {
     PinBuf<unsigned char> h_cand;
     DevBuf<float> d_desc;
     DevBuf<unsigned char> d_group;  // workspace of the device groupRectangles (group.cu)
+    PinBuf<int> h_post;             // batch path, device post-processing: [total, per-segment counts][rects]
+    DevBuf<uint8_t> d_roi_level, d_roi_pad;    // ROI path: the resized level and its reflect-101 padded copy
+    Plan plan_roi;                             // single-level plan of the padded ROI level
+    BatchJob jobs[2];                          // asynchronous batches in flight (ticket = index)
+    cudaStream_t post_stream = nullptr;        // device tails of asynchronous batches (runs beside the next batch's kernels)
+    cudaEvent_t post_done = nullptr;
     Plan plan, plan1, plan_grp;     // multi-scale plan, single-scale plan, multi-scale plan of the batch path (frame groups)
     Plan plan_part[kMaxGroup];      // batch path: plans sized for the smaller groups (lead-in, ragged last group)
     // timing
@@ -512,9 +542,14 @@ struct GroupTrace {
 };
 GroupTrace g_trace;
 
+// where a pass appends its candidates: [16-byte header: counter][Candidate * cap] in device memory
+struct CandTarget { unsigned char* p; size_t cap; };
+
 int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, const int* slots, float thresh,
-                float* d_scores, int tag, int* launches)
+                float* d_scores, int tag, int* launches, const CandTarget* target = nullptr)
 {
+    const CandTarget own{h->d_cand.p, h->cand_cap};
+    const CandTarget& ct = target ? *target : own;
     cudaStream_t st = h->stream;
     FrameSet fs; memset(&fs, 0, sizeof fs);
     for (int i = 0; i < nframes; i++) { fs.base[i] = f[i].dev; fs.pitch[i] = f[i].pitch; }
@@ -540,9 +575,9 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
         sp.ndet = ndet;
         for (int d = 0; d < ndet; d++) { sp.det[d] = h->d_det[slots[d]].p; sp.bias[d] = h->bias[slots[d]]; }
         sp.thresh = thresh; sp.scores = d_scores; sp.score_plane = P.score_floats;
-        sp.cand = reinterpret_cast<Candidate*>(h->d_cand.p + 16);
-        sp.cand_count = reinterpret_cast<unsigned int*>(h->d_cand.p);
-        sp.cand_cap = (unsigned int)h->cand_cap; sp.tag = tag;
+        sp.cand = reinterpret_cast<Candidate*>(ct.p + 16);
+        sp.cand_count = reinterpret_cast<unsigned int*>(ct.p);
+        sp.cand_cap = (unsigned int)ct.cap; sp.tag = tag;
         launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, P.d_sitems2.p, P.n_svm2, h->d_hist.p, sp, h->num_sms, st);
         (*launches) += ndet >= 2 && P.n_svm2 ? (ndet + 1) / 2 : ndet;
         g_watchdog.mark(st, "svm", nframes);
@@ -768,6 +803,8 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->post_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->post_done, cudaEventDisableTiming);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&h->up_done[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->fr_done[i], cudaEventDisableTiming);
@@ -795,8 +832,9 @@ void hogb200_destroy(hogb200_t* h)
     for (auto& b : h->d_frame) b.release();
     for (auto& b : h->d_raw) b.release();
     h->d_pyr.release(); h->d_hist.release();
-    h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release(); h->d_group.release();
-    std::vector<Plan*> plans = {&h->plan, &h->plan1, &h->plan_grp};
+    h->d_scores.release(); h->d_queue.release(); h->d_cand.release(); h->h_cand.release(); h->d_desc.release(); h->d_group.release(); h->h_post.release();
+    std::vector<Plan*> plans = {&h->plan, &h->plan1, &h->plan_grp, &h->plan_roi};
+    h->d_roi_level.release(); h->d_roi_pad.release();
     for (Plan& P : h->plan_part) plans.push_back(&P);
     for (Plan* P : plans) {
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
@@ -804,6 +842,9 @@ void hogb200_destroy(hogb200_t* h)
     }
     for (int i = 0; i < 2; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
     for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (BatchJob& J : h->jobs) { J.d_cand.release(); J.h_counts.release(); for (cudaEvent_t e : J.events) cudaEventDestroy(e); }
+    if (h->post_stream) cudaStreamDestroy(h->post_stream);
+    if (h->post_done) cudaEventDestroy(h->post_done);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     delete h;
@@ -923,6 +964,97 @@ int hogb200_create_from_file(const char* filename, const char* objname, int devi
 
 namespace {
 
+// chunks with at least this many candidates keep them on the device: ordering, rect scaling and groupRectangles of all
+// (frame, detector) segments run there (group.cu cand_group_device); smaller lists take the host path.  HOGB200_GPU_POST_MIN
+// overrides (0 = never on the device, 1 = always).
+size_t gpu_post_min()
+{
+    const char* e = getenv("HOGB200_GPU_POST_MIN");       // read per call: the tests switch paths inside one process
+    return e ? (size_t)atoll(e) : (size_t)1024;
+}
+
+// header of the candidate buffer only: the number of candidates the chunk produced
+int fetch_candidate_count(hogb200* h, size_t* count)
+{
+    cudaStream_t st = h->stream;
+    CK(h->h_cand.reserve(16 + 4096 * sizeof(Candidate)));
+    CK(cudaMemcpyAsync(h->h_cand.p, h->d_cand.p, 16, cudaMemcpyDeviceToHost, st));
+    g_watchdog.drain(st);
+    CK(cudaStreamSynchronize(st));
+    *count = *reinterpret_cast<unsigned int*>(h->h_cand.p);
+    return HOGB200_OK;
+}
+
+// The rest of a chunk's candidate list (the header is already on the host).
+int fetch_candidate_list(hogb200* h, size_t n, std::vector<Candidate>& out)
+{
+    cudaStream_t st = h->stream;
+    CK(h->h_cand.reserve(16 + n * sizeof(Candidate)));
+    if (n) {
+        CK(cudaMemcpyAsync(h->h_cand.p + 16, h->d_cand.p + 16, n * sizeof(Candidate), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    const Candidate* c = reinterpret_cast<const Candidate*>(h->h_cand.p + 16);
+    out.assign(c, c + n);
+    return HOGB200_OK;
+}
+
+// Device tail of a chunk: n candidates in d_cand -> grouped rects of every (frame, detector) segment, appended to `all`
+// with their offsets.  One synchronisation for the counts, one for the rects.
+// host tail of a chunk: candidates -> reference order -> rects (+ grouping) per (frame, detector) segment
+int host_tail(hogb200* h, const Plan& P, std::vector<Candidate>& c, int nf, int nslots, std::vector<hogb200_rect>& all, size_t* offsets,
+              size_t* out_idx)
+{
+    std::sort(c.begin(), c.end(), cand_less);
+    std::vector<hogb200_rect> rects;
+    size_t pos = 0;
+    for (int i = 0; i < nf; i++)
+        for (int d = 0; d < nslots; d++) {
+            const int key = (i << 20) | (d << 16);
+            size_t e = pos;
+            while (e < c.size() && (c[e].level & ~0xffff) == key) e++;
+            const int rc = candidates_to_rects(h, P, c.data() + pos, e - pos, rects, nullptr);
+            if (rc) return rc;
+            pos = e;
+            all.insert(all.end(), rects.begin(), rects.end());
+            offsets[++*out_idx] = all.size();
+        }
+    return HOGB200_OK;
+}
+
+CandGeom cand_geom(const hogb200* h, const Plan& P)
+{
+    CandGeom G; memset(&G, 0, sizeof G);
+    for (size_t i = 0; i < P.lv.size(); i++) G.scale[i] = P.lv[i].scale;
+    G.win_w = h->g.win_w; G.win_h = h->g.win_h; G.stride_x = h->win_stride_x; G.stride_y = h->win_stride_y;
+    return G;
+}
+
+int post_process_device(hogb200* h, const CandGeom& G, const unsigned char* d_cand, cudaStream_t st, size_t n, int nf, int nslots,
+                        int group_threshold, std::vector<hogb200_rect>& all, size_t* offsets, size_t* out_idx)
+{
+    const int nseg = nf * nslots;
+    CK(h->d_group.reserve(cand_group_workspace_bytes((int)n, nseg)));
+    CK(h->h_post.reserve((size_t)nseg + 1 + 4 * n));
+    const int* d_out = nullptr; const int* d_hdr = nullptr;
+    if (cand_group_device(d_cand + 16, (int)n, nseg, nslots, G, group_threshold, 0.2, h->d_group.p, st, &d_out, &d_hdr))
+        return fail(HOGB200_CUDA_ERROR, std::string("candidate post-processing on the device: ") + cudaGetErrorString(cudaGetLastError()));
+    CK(cudaMemcpyAsync(h->h_post.p, d_hdr, sizeof(int) * (nseg + 1), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const size_t total = (size_t)h->h_post.p[0];
+    if (total > n) return fail(HOGB200_CUDA_ERROR, "candidate post-processing on the device: inconsistent counts");
+    int* rects = h->h_post.p + nseg + 1;
+    if (total) {
+        CK(cudaMemcpyAsync(rects, d_out, total * sizeof(hogb200_rect), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    const hogb200_rect* r = reinterpret_cast<const hogb200_rect*>(rects);
+    all.insert(all.end(), r, r + total);
+    size_t acc = offsets[*out_idx];
+    for (int sgi = 0; sgi < nseg; sgi++) { acc += (size_t)h->h_post.p[1 + sgi]; offsets[++*out_idx] = acc; }
+    return HOGB200_OK;
+}
+
 // what the SVM scoring kernel can take (svm.cu); checked before anything is queued, by every entry point that scores
 int check_svm_geometry(const hogb200* h)
 {
@@ -1012,6 +1144,59 @@ int emit(const std::vector<T>& v, T* out, size_t capacity, size_t* count)
 
 }  // namespace
 
+namespace {
+
+// Queue every frame group of a chunk (consecutive frames of one shape, plan P built for groups of `grp` frames) on the
+// handle's streams: uploads on the copy stream, double-buffered per group, kernels on the compute stream.
+int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, int nslots, const int* slots, const CandTarget* target,
+                int* launches)
+{
+    int rc;
+    cudaStream_t st = h->stream, cs = h->copy_stream;
+    int& total_launches = *launches;
+    g_trace.begin();
+    // Nothing hides the upload of the first group, so when frames come from host memory the batch opens with
+    // groups of 1 and grp - 1 frames: the kernels start after one frame's copy instead of a whole group's,
+    // and the copies (faster than the kernels per frame) stay ahead from then on.
+    bool lead_in = false;
+    for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
+    lead_in = lead_in && nf > grp && batch_lead_in();
+    for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
+        ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
+        const int b = gi & 1;                     // double-buffered staging, per group
+        FrameRef f[kMaxGroup];
+        bool any_host = false;
+        for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
+        if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
+        else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
+        g_trace.mark(0, any_host ? cs : st);
+        for (int j = 0; j < ng; j++) {
+            const hogb200_image* im = fr + g0 + j;
+            // host frames: upload on the copy stream, overlapping the previous group's kernels
+            if ((rc = stage_frame(h, im, b * kMaxGroup + j, im->on_device ? st : cs, f[j]))) return rc;
+        }
+        if (any_host) {
+            CK(cudaEventRecord(h->up_done[b], cs));
+            CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
+        }
+        g_trace.mark(1, any_host ? cs : st);
+        g_trace.mark(2, st);
+        // a group smaller than grp runs on a plan of its own size: work lists dealt for grp frames leave the
+        // persistent kernels unbalanced when most of their items belong to absent frames
+        Plan* Pg = &P;
+        if (ng != grp) {
+            Pg = &h->plan_part[ng];
+            if ((rc = build_plan(h, *Pg, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, ng))) return rc;
+        }
+        if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches, target))) return rc;
+        CK(cudaEventRecord(h->fr_done[b], st));
+        g_trace.mark(3, st);
+    }
+    return HOGB200_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 int hogb200_detect(hogb200_t* h, const hogb200_image* img, hogb200_point* hits, double* conf, size_t capacity, size_t* count)
@@ -1096,73 +1281,164 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
         if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, grp))) return rc;
         Plan& P = h->plan_grp;
         size_t cap = std::max<size_t>(h->cand_cap, 1 << 18);
+        size_t ncand = 0;
         for (int attempt = 0; attempt < 2; attempt++) {
             if ((rc = ensure_cand(h, cap))) return rc;
             CK(cudaMemsetAsync(h->d_cand.p, 0, 16, st));
-            g_trace.begin();
-            // Nothing hides the upload of the first group, so when frames come from host memory the batch opens with
-            // groups of 1 and grp - 1 frames: the kernels start after one frame's copy instead of a whole group's,
-            // and the copies (faster than the kernels per frame) stay ahead from then on.
-            bool lead_in = false;
-            for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
-            lead_in = lead_in && nf > grp && batch_lead_in();
-            for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
-                ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
-                const int b = gi & 1;                     // double-buffered staging, per group
-                FrameRef f[kMaxGroup];
-                bool any_host = false;
-                for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
-                if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
-                else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
-                g_trace.mark(0, any_host ? cs : st);
-                for (int j = 0; j < ng; j++) {
-                    const hogb200_image* im = fr + g0 + j;
-                    // host frames: upload on the copy stream, overlapping the previous group's kernels
-                    if ((rc = stage_frame(h, im, b * kMaxGroup + j, im->on_device ? st : cs, f[j]))) return rc;
-                }
-                if (any_host) {
-                    CK(cudaEventRecord(h->up_done[b], cs));
-                    CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
-                }
-                g_trace.mark(1, any_host ? cs : st);
-                g_trace.mark(2, st);
-                // a group smaller than grp runs on a plan of its own size: work lists dealt for grp frames leave the
-                // persistent kernels unbalanced when most of their items belong to absent frames
-                Plan* Pg = &P;
-                if (ng != grp) {
-                    Pg = &h->plan_part[ng];
-                    if ((rc = build_plan(h, *Pg, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, ng))) return rc;
-                }
-                if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches))) return rc;
-                CK(cudaEventRecord(h->fr_done[b], st));
-                g_trace.mark(3, st);
-            }
-            size_t n = 0;
-            rc = fetch_candidates(h, c, &n);
+            if ((rc = queue_chunk(h, P, fr, nf, grp, nslots, slots, nullptr, &total_launches))) return rc;
+            if ((rc = fetch_candidate_count(h, &ncand))) return rc;
             g_trace.print();
-            if (rc == HOGB200_CAPACITY && attempt == 0) { cap = (size_t)P.nwindows * nslots * nf + 16; continue; }
-            if (rc) return rc;
+            if (ncand > h->cand_cap && attempt == 0) { cap = (size_t)P.nwindows * nslots * nf + 16; continue; }
+            if (ncand > h->cand_cap) return fail(HOGB200_CAPACITY, "candidate list overflow");
             break;
         }
-        total_cands += c.size();
-        std::sort(c.begin(), c.end(), cand_less);
-        size_t pos = 0;
-        for (int i = 0; i < nf; i++)
-            for (int d = 0; d < nslots; d++) {
-                const int key = (i << 20) | (d << 16);
-                size_t e = pos;
-                while (e < c.size() && (c[e].level & ~0xffff) == key) e++;
-                if ((rc = candidates_to_rects(h, P, c.data() + pos, e - pos, rects, nullptr))) return rc;
-                pos = e;
-                all.insert(all.end(), rects.begin(), rects.end());
-                offsets[++out_idx] = all.size();
-            }
+        total_cands += ncand;
+        if (ncand == 0) {
+            for (int i = 0; i < nf * nslots; i++) { offsets[out_idx + 1] = offsets[out_idx]; out_idx++; }
+        } else if (gpu_post_min() > 0 && ncand >= gpu_post_min()) {
+            if ((rc = post_process_device(h, cand_geom(h, P), h->d_cand.p, st, ncand, nf, nslots, h->group_threshold, all, offsets, &out_idx))) return rc;
+        } else {
+            if ((rc = fetch_candidate_list(h, ncand, c))) return rc;
+            if ((rc = host_tail(h, P, c, nf, nslots, all, offsets, &out_idx))) return rc;
+        }
         f0 += nf;
     }
     if (h->timing) cudaEventRecord(h->ev[5], st);
     finish_timing(h, h->plan_grp, total_launches, total_cands);
     size_t cnt = 0;
     return emit(all, found, capacity, &cnt);
+}
+
+// ---- asynchronous batches: submit queues everything and returns; collect waits for that batch only and runs its tail.
+// With two batches in flight the uploads and kernels of batch k + 1 overlap the host-side tail of batch k, and the
+// device tail (group.cu) runs on its own stream beside the next batch's kernels.
+int hogb200_submit_batch(hogb200_t* h, const hogb200_image* frames, int nframes, int nslots, int* ticket)
+{
+    H_OR_FAIL;
+    if (!ticket || nframes < 0 || (nframes > 0 && !frames)) return fail(HOGB200_BAD_ARG, "bad batch arguments");
+    *ticket = -1;
+    if (nslots < 1 || nslots > kMaxDet) return fail(HOGB200_BAD_ARG, "bad nslots");
+    for (int d = 0; d < nslots; d++) if (!h->have_det[d]) return fail(HOGB200_BAD_ARG, "detector slot not set");
+    int rc;
+    if ((rc = check_work_params(h))) return rc;
+    if ((rc = check_svm_geometry(h))) return rc;
+    for (int i = 0; i < nframes; i++) if ((rc = check_image(&frames[i]))) return rc;
+    if ((rc = use_device(h))) return rc;
+    int slot = -1;
+    for (int i = 0; i < 2 && slot < 0; i++) if (!h->jobs[i].active) slot = i;
+    if (slot < 0) return fail(HOGB200_BAD_ARG, "two batches are already in flight: collect one first");
+    BatchJob& J = h->jobs[slot];
+    J.frames.assign(frames, frames + nframes);
+    J.nslots = nslots; J.launches = 0; J.chunks.clear(); J.finished = false;
+    J.hit_threshold = h->hit_threshold; J.group_threshold = h->group_threshold; J.stride_x = h->win_stride_x; J.stride_y = h->win_stride_y;
+    const int kChunk = 64;
+    for (int f0 = 0; f0 < nframes;) {
+        int nf = 1;
+        while (f0 + nf < nframes && nf < kChunk && frames[f0 + nf].width == frames[f0].width &&
+               frames[f0 + nf].height == frames[f0].height && frames[f0 + nf].channels == frames[f0].channels) nf++;
+        ChunkJob c; c.f0 = f0; c.nf = nf;
+        J.chunks.push_back(c);
+        f0 += nf;
+    }
+    const size_t nchunks = J.chunks.size();
+    // one candidate region per chunk (a chunk that overflows its region is re-run by collect)
+    const size_t cap = (size_t)1 << 18, region = align_up(16 + cap * sizeof(Candidate), 256);
+    cudaStream_t st = h->stream;
+    if (J.d_cand.cap < region * nchunks) { CK(cudaStreamSynchronize(st)); CK(cudaStreamSynchronize(h->post_stream)); }
+    CK(J.d_cand.reserve(region * nchunks));
+    CK(J.h_counts.reserve(4 * nchunks + 4));
+    while (J.events.size() < nchunks) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); J.events.push_back(e); }
+    int slots[kMaxDet] = {0, 1, 2, 3};
+    for (size_t k = 0; k < nchunks; k++) {
+        ChunkJob& c = J.chunks[k];
+        const hogb200_image* fr = &J.frames[c.f0];
+        const int cn = fr->channels == 3 ? 4 : fr->channels;
+        const int grp = std::min(batch_group(h, fr->width, fr->height, cn), c.nf);
+        if ((rc = build_plan(h, h->plan_grp, fr->width, fr->height, cn, false, grp))) return rc;
+        c.cand_off = k * region; c.cap = cap; c.lv = h->plan_grp.lv; c.nwindows = h->plan_grp.nwindows; c.done = J.events[k];
+        const CandTarget target{J.d_cand.p + c.cand_off, cap};
+        CK(cudaMemsetAsync(target.p, 0, 16, st));
+        if ((rc = queue_chunk(h, h->plan_grp, fr, c.nf, grp, nslots, slots, &target, &J.launches))) return rc;
+        CK(cudaMemcpyAsync(J.h_counts.p + 4 * k, target.p, 16, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(c.done, st));
+    }
+    J.active = true;
+    *ticket = slot;
+    return HOGB200_OK;
+}
+
+int hogb200_collect_batch(hogb200_t* h, int ticket, hogb200_rect* found, size_t capacity, size_t* offsets)
+{
+    H_OR_FAIL;
+    if (ticket < 0 || ticket >= 2 || !h->jobs[ticket].active) return fail(HOGB200_BAD_ARG, "no batch in flight under this ticket");
+    if (!offsets) return fail(HOGB200_BAD_ARG, "offsets is null");
+    BatchJob& J = h->jobs[ticket];
+    int rc;
+    if ((rc = use_device(h))) return rc;
+    if (J.finished) {                                      // a previous collect found `capacity` too small
+        memcpy(offsets, J.result_off.data(), J.result_off.size() * sizeof(size_t));
+        size_t cnt = 0;
+        rc = emit(J.result, found, capacity, &cnt);
+        if (rc != HOGB200_CAPACITY) J.active = false;
+        return rc;
+    }
+    std::vector<hogb200_rect> all; all.reserve(1024);
+    std::vector<Candidate> cands;
+    offsets[0] = 0;
+    size_t out_idx = 0, total_cands = 0;
+    const int nslots = J.nslots;
+    cudaStream_t ps = h->post_stream;
+    // the tail reads the parameters the batch was submitted with
+    const int g_now = h->group_threshold, sx_now = h->win_stride_x, sy_now = h->win_stride_y;
+    h->group_threshold = J.group_threshold; h->win_stride_x = J.stride_x; h->win_stride_y = J.stride_y;
+    auto restore = [&](int code) { h->group_threshold = g_now; h->win_stride_x = sx_now; h->win_stride_y = sy_now; J.active = false; return code; };
+    for (size_t k = 0; k < J.chunks.size(); k++) {
+        ChunkJob& c = J.chunks[k];
+        if (cudaEventSynchronize(c.done) != cudaSuccess)
+            return restore(fail(HOGB200_CUDA_ERROR, std::string("collect: ") + cudaGetErrorString(cudaGetLastError())));
+        const size_t n = J.h_counts.p[4 * k];
+        const unsigned char* d_cand = J.d_cand.p + c.cand_off;
+        Plan P; P.lv = c.lv;                               // the level scales are all the tail needs of the plan
+        if (n > c.cap) {
+            // the chunk produced more candidates than its region holds: run it again through the blocking entry
+            // point, which sizes its list to the worst case
+            std::vector<hogb200_rect> part((size_t)std::max<long long>(c.nwindows, 1) * nslots * c.nf);
+            std::vector<size_t> off((size_t)c.nf * nslots + 1);
+            const double hit_now = h->hit_threshold; h->hit_threshold = J.hit_threshold;
+            rc = hogb200_detect_multiscale_batch(h, &J.frames[c.f0], c.nf, nslots, part.data(), part.size(), off.data());
+            h->hit_threshold = hit_now;
+            if (rc) return restore(rc);
+            const size_t base = all.size();
+            all.insert(all.end(), part.begin(), part.begin() + off.back());
+            for (size_t i = 1; i < off.size(); i++) offsets[++out_idx] = base + off[i];
+            total_cands += (size_t)h->last.candidates;
+            continue;
+        }
+        total_cands += n;
+        if (n == 0) {
+            for (int i = 0; i < c.nf * nslots; i++) { offsets[out_idx + 1] = offsets[out_idx]; out_idx++; }
+        } else if (gpu_post_min() > 0 && n >= gpu_post_min()) {
+            if ((rc = post_process_device(h, cand_geom(h, P), d_cand, ps, n, c.nf, nslots, J.group_threshold, all, offsets, &out_idx)))
+                return restore(rc);
+        } else {
+            cudaError_t e = h->h_cand.reserve(16 + n * sizeof(Candidate));
+            if (e == cudaSuccess) e = cudaMemcpyAsync(h->h_cand.p + 16, d_cand + 16, n * sizeof(Candidate), cudaMemcpyDeviceToHost, ps);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ps);
+            if (e != cudaSuccess) { cudaGetLastError(); return restore(fail(HOGB200_CUDA_ERROR, std::string("collect: ") + cudaGetErrorString(e))); }
+            const Candidate* cp = reinterpret_cast<const Candidate*>(h->h_cand.p + 16);
+            cands.assign(cp, cp + n);
+            if ((rc = host_tail(h, P, cands, c.nf, nslots, all, offsets, &out_idx))) return restore(rc);
+        }
+    }
+    h->last = hogb200_timings{};
+    h->last.kernel_launches = J.launches; h->last.candidates = (long long)total_cands;
+    size_t cnt = 0;
+    rc = restore(emit(all, found, capacity, &cnt));
+    if (rc == HOGB200_CAPACITY) {                          // keep the results: collect again with all.size() entries
+        J.result.swap(all); J.result_off.assign(offsets, offsets + out_idx + 1);
+        J.finished = true; J.active = true;
+    }
+    return rc;
 }
 
 }  // extern "C"
@@ -1307,6 +1583,175 @@ int hogb200_block_histograms(hogb200_t* h, const hogb200_image* img, float* out,
         CK(cudaStreamSynchronize(h->stream));
     }
     return HOGB200_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// One level of the frame, device resident: the frame itself when the size matches (hog.cpp:3522-3525), else
+// cv::resize INTER_LINEAR semantics into h->d_roi_level (the mandated pyramid resize; the CPU class uses
+// INTER_LINEAR_EXACT here).
+int roi_level_image(hogb200* h, const FrameRef& f, int W, int H, int cn, int dw, int dh, FrameRef& out)
+{
+    if (dw == W && dh == H) { out = f; return HOGB200_OK; }
+    cudaStream_t st = h->stream;
+    LevelDesc D; memset(&D, 0, sizeof D);
+    D.w = dw; D.h = dh; D.pitch = (int)align_up((size_t)dw * cn, 64);
+    D.mode = is_exact_half(W, H, dw, dh) ? 2 : 1;
+    std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
+    if (D.mode == 1) { resize_table(W, dw, true, xt); resize_table(H, dh, false, yt); }
+    if (D.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(xt.data(), dw, yt.data(), dh, W);
+    const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
+    for (int y = 0; y < dh; y += th) for (int x = 0; x < dw; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
+    CK(cudaStreamSynchronize(st));          // the tables below are freed at the end of this call: nothing may still read older ones
+    CK(h->d_roi_level.reserve((size_t)D.pitch * dh + 64));
+    D.img = h->d_roi_level.p;
+    DevBuf<LevelDesc> d_lv; DevBuf<ResizeCoef> d_xt, d_yt; DevBuf<ResizeItem> d_it;
+    cudaError_t e = d_lv.reserve(1);
+    if (e == cudaSuccess) e = d_xt.reserve(xt.size() + 1);
+    if (e == cudaSuccess) e = d_yt.reserve(yt.size() + 1);
+    if (e == cudaSuccess) e = d_it.reserve(items.size() + 1);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_lv.p, &D, sizeof D, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && !xt.empty()) e = cudaMemcpyAsync(d_xt.p, xt.data(), xt.size() * sizeof(ResizeCoef), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && !yt.empty()) e = cudaMemcpyAsync(d_yt.p, yt.data(), yt.size() * sizeof(ResizeCoef), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_it.p, items.data(), items.size() * sizeof(ResizeItem), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        FrameSet fs; memset(&fs, 0, sizeof fs);
+        fs.base[0] = f.dev; fs.pitch[0] = f.pitch; fs.nframes = 1;
+        launch_resize(fs, W, H, cn, d_lv.p, d_xt.p, d_yt.p, d_it.p, (int)items.size(), st);
+        e = cudaGetLastError();
+    }
+    cudaError_t e2 = cudaStreamSynchronize(st);
+    d_lv.release(); d_xt.release(); d_yt.release(); d_it.release();
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(HOGB200_CUDA_ERROR, std::string("roi level resize: ") + cudaGetErrorString(e)); }
+    out.dev = h->d_roi_level.p; out.pitch = D.pitch;
+    return HOGB200_OK;
+}
+
+// HOGDescriptor::detectROI (objdetect/src/hog.cpp:3549-3660) on a device-resident level image of lw x lh pixels.
+// The CPU class scores windows on the image PADDED by (pad_w, pad_h) with BORDER_REFLECT_101 gradients; here the level is
+// materialised with a frame of pad + 8 pixels (one block more than the padding, so that every gradient the padded
+// grid needs has both neighbours inside the materialised image: its values equal the reference's xmap/ymap look-ups),
+// histograms and dense stride-8 scores are computed by the usual two kernels, and the requested locations are read
+// out of the score plane.  conf gets one entry per location (-10.0 = outside the padded image, hog.cpp:3596-3602).
+int roi_score_level(hogb200* h, int slot, const FrameRef& lv, int lw, int lh, int cn, const hogb200_point* loc, size_t n,
+                    int pad_w, int pad_h, std::vector<double>& conf, std::vector<float>& plane)
+{
+    const int cs = kCell;                               // cacheStride = gcd(winStride = cellSize, blockStride) = 8
+    pad_w = (int)align_up((size_t)std::max(pad_w, 0), cs); pad_h = (int)align_up((size_t)std::max(pad_h, 0), cs);
+    conf.assign(n, -10.0);
+    const int win_w = h->g.win_w, win_h = h->g.win_h;
+    bool any = false;
+    for (size_t i = 0; i < n; i++) {
+        const hogb200_point p = loc[i];
+        if (p.x < -pad_w || p.x > lw + pad_w - win_w || p.y < -pad_h || p.y > lh + pad_h - win_h) continue;
+        if (p.x % cs != 0 || p.y % cs != 0)
+            return fail(HOGB200_BAD_ARG, "detectROI: locations must be multiples of the cache stride 8 (HOGCache::getBlock asserts, hog.cpp:918)");
+        any = true;
+    }
+    if (!any) return HOGB200_OK;
+    const int px = pad_w + kCell, py = pad_h + kCell;
+    const int mw = lw + 2 * px, mh = lh + 2 * py;
+    const size_t mpitch = align_up((size_t)mw * cn, 64);
+    int rc;
+    CK(cudaStreamSynchronize(h->stream));
+    CK(h->d_roi_pad.reserve(mpitch * mh + 64));
+    launch_pad_reflect101(lv.dev, (size_t)lv.pitch, lw, lh, cn, h->d_roi_pad.p, mpitch, px, py, h->stream);
+    CK(cudaGetLastError());
+    hogb200_image im; im.data = h->d_roi_pad.p; im.pitch = mpitch; im.width = mw; im.height = mh; im.channels = cn; im.on_device = 1;
+    // dense scores of the materialised level at window stride 8 x 8, whatever the handle's stride is
+    const int sx = h->win_stride_x, sy = h->win_stride_y;
+    h->win_stride_x = h->win_stride_y = kCell;
+    std::vector<Candidate> c;
+    rc = build_plan(h, h->plan_roi, mw, mh, cn, true);
+    size_t np = 0;
+    if (!rc) {
+        np = (size_t)h->plan_roi.lv[0].nwx * h->plan_roi.lv[0].nwy;
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e == cudaSuccess) e = h->d_scores.reserve(np + 16);
+        if (e != cudaSuccess) rc = fail(HOGB200_CUDA_ERROR, cudaGetErrorString(e));
+    }
+    if (!rc && np) rc = run_single(h, h->plan_roi, &im, true, 1, &slot, INFINITY, h->d_scores.p, c);
+    h->win_stride_x = sx; h->win_stride_y = sy;
+    if (rc) return rc;
+    if (!np) return HOGB200_OK;
+    plane.resize(np);
+    CK(cudaMemcpyAsync(plane.data(), h->d_scores.p, np * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    const int nwx = h->plan_roi.lv[0].nwx;
+    for (size_t i = 0; i < n; i++) {
+        const hogb200_point p = loc[i];
+        if (p.x < -pad_w || p.x > lw + pad_w - win_w || p.y < -pad_h || p.y > lh + pad_h - win_h) continue;
+        conf[i] = (double)plane[(size_t)((p.y + py) / kCell) * nwx + (p.x + px) / kCell];
+    }
+    return HOGB200_OK;
+}
+
+int roi_prepare(hogb200* h, const hogb200_image* img, FrameRef& f, int* cn)
+{
+    int rc;
+    if ((rc = check_image(img))) return rc;
+    if ((rc = check_svm_geometry(h))) return rc;
+    if ((rc = use_device(h))) return rc;
+    if ((rc = stage_frame(h, img, 0, h->stream, f))) return rc;
+    *cn = img->channels == 3 ? 4 : img->channels;
+    return HOGB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hogb200_detect_roi(hogb200_t* h, const hogb200_image* img, const hogb200_point* locations, size_t n, int pad_w, int pad_h,
+                       hogb200_point* found, double* confidences, size_t capacity, size_t* count)
+{
+    H_OR_FAIL;
+    if (count) *count = 0;
+    if (n && !locations) return fail(HOGB200_BAD_ARG, "null locations");
+    if (!h->have_det[0] || n == 0) { int rc = check_image(img); return rc; }          // hog.cpp:3558-3559
+    FrameRef f; int cn = 0, rc;
+    if ((rc = roi_prepare(h, img, f, &cn))) return rc;
+    std::vector<double> conf; std::vector<float> plane;
+    if ((rc = roi_score_level(h, 0, f, img->width, img->height, cn, locations, n, pad_w, pad_h, conf, plane))) return rc;
+    if (confidences) memcpy(confidences, conf.data(), n * sizeof(double));
+    std::vector<hogb200_point> hits;
+    for (size_t i = 0; i < n; i++) if (conf[i] != -10.0 && conf[i] >= h->hit_threshold) hits.push_back(locations[i]);
+    return emit(hits, found, capacity, count);
+}
+
+int hogb200_detect_multiscale_roi(hogb200_t* h, const hogb200_image* img, hogb200_roi* rois, size_t nrois, int group_threshold,
+                                  hogb200_rect* found, size_t capacity, size_t* count)
+{
+    H_OR_FAIL;
+    if (count) *count = 0;
+    if (nrois && !rois) return fail(HOGB200_BAD_ARG, "null rois");
+    for (size_t i = 0; i < nrois; i++)
+        if (!(rois[i].scale > 0) || !std::isfinite(rois[i].scale) || (rois[i].nlocations && !rois[i].locations))
+            return fail(HOGB200_BAD_ARG, "bad roi (scale must be positive, locations non-null)");
+    if (!h->have_det[0] || nrois == 0) return check_image(img);
+    FrameRef f; int cn = 0, rc;
+    if ((rc = roi_prepare(h, img, f, &cn))) return rc;
+    const int W = img->width, H = img->height;
+    std::vector<hogb200_rect> all; std::vector<double> conf; std::vector<float> plane;
+    for (size_t i = 0; i < nrois; i++) {
+        hogb200_roi& R = rois[i];
+        if (R.nlocations == 0) continue;                                         // detectROI returns at once (hog.cpp:3558)
+        const double scale = R.scale;
+        const int lw = cvRound(W / scale), lh = cvRound(H / scale);             // HOGConfInvoker, hog.cpp:3518-3520
+        if (lw <= 0 || lh <= 0) return fail(HOGB200_BAD_ARG, "roi scale leaves an empty image");
+        FrameRef lv;
+        if ((rc = roi_level_image(h, f, W, H, cn, lw, lh, lv))) return rc;
+        if ((rc = roi_score_level(h, 0, lv, lw, lh, cn, R.locations, R.nlocations, 8, 8, conf, plane))) return rc;   // padding 8 x 8, hog.cpp:3672
+        if (R.confidences) memcpy(R.confidences, conf.data(), R.nlocations * sizeof(double));
+        const int sw = cvRound(h->g.win_w * scale), sh = cvRound(h->g.win_h * scale);
+        for (size_t j = 0; j < R.nlocations; j++)
+            if (conf[j] != -10.0 && conf[j] >= h->hit_threshold)
+                all.push_back(hogb200_rect{cvRound(R.locations[j].x * scale), cvRound(R.locations[j].y * scale), sw, sh});
+    }
+    if (group_threshold > 0 && (rc = group_rectangles_auto(h, all, group_threshold, 0.2))) return rc;
+    return emit(all, found, capacity, count);
 }
 
 size_t hogb200_noalloc_scratch_bytes(void) { return hist_noalloc_scratch_bytes(); }

@@ -75,6 +75,9 @@ int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int 
 // 8UC3 (B,G,R) -> 8UC4 (B,G,R,255): the colour conversion example_gpu_tbd does on the host before the upload
 // (samples/gpu/tbd.cpp:573-599), moved to the device.  dst rows are 16-byte aligned.
 void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st);
+// dst = src with a BORDER_REFLECT_101 frame of px / py pixels (cn = 1 or 4; 4-byte aligned rows for cn = 4)
+void launch_pad_reflect101(const uint8_t* src, size_t spitch, int w, int h, int cn, uint8_t* dst, size_t dpitch, int px, int py,
+                           cudaStream_t st);
 void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
                    const LevelDesc* d_levels, const ResizeCoef* d_xtab, const ResizeCoef* d_ytab,
                    const ResizeItem* d_items, int nitems, cudaStream_t st);
@@ -125,6 +128,13 @@ void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_
 // reference's input order; returns the number of grouped rects written to h_out, -1 on a CUDA error
 size_t group_workspace_bytes(int n);
 int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int* h_out, void* ws, cudaStream_t st);
+
+// The tail of detectMultiScale for all (frame, detector) segments of a chunk on the device (group.cu): candidate list ->
+// reference order -> scaled rects -> groupRectangles per segment.  Nothing is synchronised; see group.cu.
+struct CandGeom { double scale[kMaxLevels]; int win_w, win_h, stride_x, stride_y; };
+size_t cand_group_workspace_bytes(int n, int nseg);
+int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandGeom& G, int thr, double eps, void* ws,
+                      cudaStream_t st, const int** d_out_p, const int** d_hdr_p);
 
 int hist_tile_blocks_x();   // blocks per tile in x (14)
 int hist_strip_blocks_y();  // block rows per strip: 0 = let the host choose, else the HOGB200_STRIP override

@@ -423,6 +423,26 @@ bgr_to_bgra_kernel(const uint8_t* __restrict__ src, size_t spitch, uint8_t* __re
     }
 }
 
+// Image + border, BORDER_REFLECT_101 (cv::borderInterpolate, core/src/copy.cpp): dst(y, x) = src(r(y - py), r(x - px)).
+// One thread per destination pixel (BPP = bytes per pixel, 1 or 4).  Feeds the ROI path, whose windows may reach into
+// the padding the CPU class puts around an image (objdetect/src/hog.cpp:3566-3570).
+__device__ __forceinline__ int reflect101(int p, int len)
+{
+    if (len == 1) return 0;
+    while ((unsigned)p >= (unsigned)len) p = p < 0 ? -p : 2 * len - 2 - p;
+    return p;
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+pad_reflect101_kernel(const uint8_t* __restrict__ src, size_t spitch, int w, int h, uint8_t* __restrict__ dst, size_t dpitch,
+                      int px, int py)
+{
+    const int x = blockIdx.x * 64 + (threadIdx.x & 63), y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (x >= w + 2 * px || y >= h + 2 * py) return;
+    const T v = reinterpret_cast<const T*>(src + (size_t)reflect101(y - py, h) * spitch)[reflect101(x - px, w)];
+    reinterpret_cast<T*>(dst + (size_t)y * dpitch)[x] = v;
+}
+
 }  // namespace
 
 void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st)
@@ -430,6 +450,14 @@ void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t 
     if (w <= 0 || h <= 0) return;
     const int aligned = ((uintptr_t)src % 4 == 0) && (spitch % 4 == 0);
     bgr_to_bgra_kernel<<<dim3((w + 255) / 256, (h + 3) / 4), 256, 0, st>>>(src, spitch, dst, dpitch, w, h, aligned);
+}
+
+void launch_pad_reflect101(const uint8_t* src, size_t spitch, int w, int h, int cn, uint8_t* dst, size_t dpitch, int px, int py,
+                           cudaStream_t st)
+{
+    const dim3 grid((w + 2 * px + 63) / 64, (h + 2 * py + 3) / 4);
+    if (cn == 4) pad_reflect101_kernel<unsigned><<<grid, 256, 0, st>>>(src, spitch, w, h, dst, dpitch, px, py);
+    else pad_reflect101_kernel<uint8_t><<<grid, 256, 0, st>>>(src, spitch, w, h, dst, dpitch, px, py);
 }
 
 // HOGB200_RS_DIRECT=1: every 8UC4 level through the unstaged kernel (64 x 64 tiles)

@@ -40,6 +40,10 @@ class _Model(C.Structure):
                 ("gamma_correction", C.c_int), ("nlevels", C.c_int)]
 
 
+class _Roi(C.Structure):
+    _fields_ = [("scale", C.c_double), ("locations", C.c_void_p), ("nlocations", C.c_size_t), ("confidences", C.c_void_p)]
+
+
 class Timings(C.Structure):
     _fields_ = [("upload_ms", C.c_float), ("resize_ms", C.c_float), ("hist_ms", C.c_float), ("svm_ms", C.c_float),
                 ("download_ms", C.c_float), ("total_ms", C.c_float), ("kernel_launches", C.c_int),
@@ -87,6 +91,8 @@ def load_library():
                                                  C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_detect_multiscale_batch.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_int, C.c_int, C.c_void_p,
                                                   C.c_size_t, C.c_void_p]
+    L.hogb200_submit_batch.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_int, C.c_int, C.POINTER(C.c_int)]
+    L.hogb200_collect_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
     L.hogb200_compute.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_size_t)]
     L.hogb200_levels.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                  C.POINTER(C.c_size_t)]
@@ -104,6 +110,10 @@ def load_library():
     L.hogb200_group_rectangles_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.POINTER(C.c_size_t)]
     L.hogb200_group_rectangles_meanshift.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_int, C.c_int,
                                                      C.POINTER(C.c_size_t)]
+    L.hogb200_detect_roi.argtypes = [C.c_void_p, C.POINTER(_Image), C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.c_size_t, C.POINTER(C.c_size_t)]
+    L.hogb200_detect_multiscale_roi.argtypes = [C.c_void_p, C.POINTER(_Image), C.POINTER(_Roi), C.c_size_t, C.c_int, C.c_void_p,
+                                                C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_batch_group.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     L.hogb200_model_read.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     L.hogb200_model_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(_Model), C.c_void_p, C.c_size_t]
@@ -313,6 +323,56 @@ class HOG:
             self._ck(rc)
             offs = offs.astype(np.int64)
             return [r[offs[i]:offs[i + 1]].copy() for i in range(len(frames) * nslots)]
+
+    def detectROI(self, img, locations, padding=(8, 8)):
+        """cv::HOGDescriptor::detectROI -> (found (M,2) int32, confidences (len(locations),) float64)"""
+        keep = []; im = _as_image(img, keep)
+        loc = np.ascontiguousarray(np.asarray(locations, np.int32).reshape(-1, 2))
+        found = np.zeros((max(len(loc), 1), 2), np.int32); conf = np.zeros(max(len(loc), 1), np.float64); n = C.c_size_t()
+        self._ck(self._L.hogb200_detect_roi(self._h, C.byref(im), loc.ctypes.data, len(loc), int(padding[0]), int(padding[1]),
+                                            found.ctypes.data, conf.ctypes.data, len(found), C.byref(n)))
+        return found[:n.value].copy(), conf[:len(loc)].copy()
+
+    def detectMultiScaleROI(self, img, rois, group_threshold=0):
+        """cv::HOGDescriptor::detectMultiScaleROI.  rois: list of (scale, (K,2) locations in that level's pixels)
+        -> (rects (M,4) int32, [confidences (K,) per roi])"""
+        keep = []; im = _as_image(img, keep)
+        locs = [np.ascontiguousarray(np.asarray(r[1], np.int32).reshape(-1, 2)) for r in rois]
+        confs = [np.zeros(max(len(l), 1), np.float64) for l in locs]
+        arr = (_Roi * max(len(rois), 1))(*[_Roi(float(r[0]), l.ctypes.data, len(l), c.ctypes.data) for r, l, c in zip(rois, locs, confs)])
+        cap = max(sum(len(l) for l in locs), 1)
+        out = np.zeros((cap, 4), np.int32); n = C.c_size_t()
+        self._ck(self._L.hogb200_detect_multiscale_roi(self._h, C.byref(im), arr, len(rois), int(group_threshold), out.ctypes.data,
+                                                       cap, C.byref(n)))
+        return out[:n.value].copy(), [c[:len(l)].copy() for c, l in zip(confs, locs)]
+
+    def submitBatch(self, frames, nslots=1):
+        """hogb200_submit_batch: queue the batch, return a ticket for collectBatch (at most two in flight)."""
+        keep = []
+        arr = (_Image * len(frames))(*[_as_image(f, keep) for f in frames])
+        t = C.c_int(-1)
+        self._ck(self._L.hogb200_submit_batch(self._h, arr, len(frames), nslots, C.byref(t)))
+        if not hasattr(self, "_inflight"):
+            self._inflight = {}
+        self._inflight[t.value] = (keep, arr, len(frames) * nslots)      # the frames stay alive until the batch is collected
+        return t.value
+
+    def collectBatch(self, ticket, capacity=1 << 16):
+        """hogb200_collect_batch -> list (frame-major, slot-minor) of (N,4) int32 rect arrays."""
+        keep, arr, nseg = self._inflight[ticket]
+        while True:
+            r = getattr(self, "_rect_buf", None)
+            if r is None or len(r) < capacity:
+                r = self._rect_buf = np.empty((capacity, 4), np.int32)
+            offs = np.zeros(nseg + 1, np.uint64)
+            rc = self._L.hogb200_collect_batch(self._h, ticket, r.ctypes.data, capacity, offs.ctypes.data)
+            if rc == 3:                   # the results are kept by the library: collect again with room for them
+                capacity = max(int(offs[-1]), 8 * capacity); continue
+            break
+        del self._inflight[ticket]
+        self._ck(rc)
+        offs = offs.astype(np.int64)
+        return [r[offs[i]:offs[i + 1]].copy() for i in range(nseg)]
 
     def compute(self, img):
         """-> descriptors (windows, descriptor_size) float32"""

@@ -530,6 +530,158 @@ def test_full_size_kitti_sequence_two_detectors(hog, port):
         hog.setNumLevels(64); hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
 
 
+def test_batch_tail_on_device_equals_host_tail(hog, port, monkeypatch):
+    """The batch entry point's tail (reference order, rect scaling, groupRectangles per (frame, detector)) computed on
+    the device for the whole chunk (group.cu cand_group_device) against the host tail, forced either way: identical
+    rects in identical order, grouped and ungrouped, one and two detectors, ragged groups; and against the oracle."""
+    rng = np.random.RandomState(21)
+    veh = (rng.randn(3781) * 0.05).astype(np.float32); veh[3780] = -0.5
+    det = hog.getDefaultPeopleDetector()
+    hog.setSVMDetector(veh, slot=1)
+    frames = [synthetic_frame(9100 + i, 640, 480, 4, silhouettes=4) for i in range(11)]
+    try:
+        for hit, group, nslots in ((-1.5, 2, 1), (-1.5, 0, 2), (-2.5, 3, 2), (-0.5, 2, 2), (5.0, 2, 1)):
+            hog.setHitThreshold(hit); hog.setGroupThreshold(group)
+            monkeypatch.setenv("HOGB200_GPU_POST_MIN", "0")
+            host = hog.detectMultiScaleBatch(frames, nslots=nslots)
+            monkeypatch.setenv("HOGB200_GPU_POST_MIN", "1")
+            dev = hog.detectMultiScaleBatch(frames, nslots=nslots)
+            assert len(host) == len(dev) == len(frames) * nslots
+            assert all(np.array_equal(a, b) for a, b in zip(host, dev)), (hit, group, nslots)
+            assert hit > 0 or sum(len(a) for a in dev) > 0
+            assert hog.lastTimings()["candidates"] > 0 or hit > 0
+        monkeypatch.setenv("HOGB200_GPU_POST_MIN", "1")
+        for slot, d in ((0, det), (1, veh)):
+            ok, got, exp = detections_match(hog, port, frames[3], d, -1.5, 2, slot=slot)
+            hog.setHitThreshold(-1.5); hog.setGroupThreshold(2)
+            assert ok and np.array_equal(hog.detectMultiScaleBatch(frames[:5], nslots=2)[2 * 3 + slot], got)
+    finally:
+        hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+def test_submit_collect_equals_blocking_batch(hog, monkeypatch):
+    """hogb200_submit_batch / hogb200_collect_batch: two batches in flight, collected in and out of order, host and
+    device frames, host and device tails, a candidate region that overflows (re-run by collect), a too small output
+    array (results kept for the next collect): always the blocking entry point's output."""
+    import torch
+    from opencv_b200 import HogError
+    a = [synthetic_frame(9300 + i, 640, 480, 4, silhouettes=4) for i in range(9)]
+    b = [synthetic_frame(9400 + i, 1242, 375, 4, silhouettes=3) for i in range(6)]
+    bd = [torch.from_numpy(f).cuda() for f in b]
+    try:
+        for hit, group, post in ((-1.5, 2, "0"), (-1.5, 2, "1"), (-2.0, 0, "1"), (3.0, 2, "1")):
+            monkeypatch.setenv("HOGB200_GPU_POST_MIN", post)
+            hog.setHitThreshold(hit); hog.setGroupThreshold(group)
+            wa = hog.detectMultiScaleBatch(a); wb = hog.detectMultiScaleBatch(b)
+            t0 = hog.submitBatch(a); t1 = hog.submitBatch(bd)
+            with pytest.raises(HogError):
+                hog.submitBatch(a)                                   # a third batch has to wait
+            gb = hog.collectBatch(t1); ga = hog.collectBatch(t0)     # out of order
+            assert all(np.array_equal(x, y) for x, y in zip(ga, wa)) and all(np.array_equal(x, y) for x, y in zip(gb, wb))
+            t0 = hog.submitBatch(a + b)                              # two shapes in one batch: two chunks
+            t1 = hog.submitBatch(b)
+            g0 = hog.collectBatch(t0, capacity=4); g1 = hog.collectBatch(t1)
+            assert all(np.array_equal(x, y) for x, y in zip(g0, wa + wb)) and all(np.array_equal(x, y) for x, y in zip(g1, wb))
+        # every window a candidate: 9 VGA frames x 25 132 windows < the 262 144-candidate region; 1242x375 x 6 = 201 216 too --
+        # 4K-sized demand comes from 64 frames: here force the overflow with a 40-frame VGA batch (1 005 280 candidates)
+        hog.setHitThreshold(-100.0); hog.setGroupThreshold(0)
+        many = [a[i % len(a)] for i in range(40)]
+        want = hog.detectMultiScaleBatch(many, capacity=1 << 21)
+        got = hog.collectBatch(hog.submitBatch(many), capacity=1 << 21)
+        assert sum(len(x) for x in got) == 40 * 25132 and all(np.array_equal(x, y) for x, y in zip(got, want))
+    finally:
+        hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
+# ------------------------------------------------------------------ ROI variants (row f4)
+def _roi_locations(rng, w, h, n, pad=8, win=(64, 128)):
+    """window origins on the 8-pixel lattice: inside the image, reaching into the padding, and a few outside it"""
+    xs = rng.randint(-pad // 8 - 1, (w + pad - win[0]) // 8 + 3, n) * 8
+    ys = rng.randint(-pad // 8 - 1, (h + pad - win[1]) // 8 + 3, n) * 8
+    return np.stack([xs, ys], 1).astype(np.int32)
+
+
+@pytest.mark.parametrize("cn,shape", [(1, (320, 240)), (4, (333, 251)), (4, (640, 480))])
+def test_detect_roi_vs_unmodified_reference(hog, cn, shape):
+    """cv::HOGDescriptor::detectROI of the unmodified reference (objdetect/src/hog.cpp:3549-3660), padding 8 x 8 and 0 x 0 and
+    16 x 24: confidences within 1e-3 for every location (windows reaching into the reflect-101 padding included), -10 for
+    the locations outside, the same hits modulo the threshold tolerance."""
+    if not Ref.available():
+        pytest.skip("oracle/_ref not present")
+    ref = Ref()
+    W, H = shape
+    img = synthetic_frame(70 + cn + W, W, H, cn, silhouettes=3)
+    det = hog.getDefaultPeopleDetector()
+    rng = np.random.RandomState(W)
+    for pad in ((8, 8), (0, 0), (16, 24)):
+        loc = _roi_locations(rng, W, H, 300, max(pad))
+        _, ec0 = ref.detect_roi(img, det, loc, hit_threshold=0.0, padding=pad)
+        thr = float(np.percentile(ec0[ec0 != -10.0], 80))
+        ef, ec = ref.detect_roi(img, det, loc, hit_threshold=thr, padding=pad)
+        hog.setHitThreshold(thr)
+        gf, gc = hog.detectROI(img, loc, padding=pad)
+        assert np.array_equal(gc == -10.0, ec == -10.0) and (ec == -10.0).any() and (ec != -10.0).sum() > 100
+        assert np.abs(gc - ec).max() <= SCORE_TOL, float(np.abs(gc - ec).max())
+        near = np.abs(ec - thr) <= SCORE_TOL
+        sure = set(map(tuple, loc[(ec >= thr) & ~near & (ec != -10.0)])); maybe = set(map(tuple, loc[near]))
+        assert sure <= set(map(tuple, gf)) <= sure | maybe and len(gf) > 0 and len(ef) > 0
+    hog.setHitThreshold(0.0)
+    from opencv_b200 import HogError
+    with pytest.raises(HogError):
+        hog.detectROI(img, [[12, 8]])                       # not on the cache-stride lattice: the reference asserts too
+    assert len(hog.detectROI(img, np.zeros((0, 2), np.int32))[0]) == 0
+
+
+def test_detect_multiscale_roi(hog, port):
+    """cv::HOGDescriptor::detectMultiScaleROI.  (a) scale 1 only -- no resize involved -- against the unmodified function
+    end to end, grouped and ungrouped; (b) several scales against the reference's own detectROI applied to the mandated
+    INTER_LINEAR levels (the oracle convention of DESIGN.md section 2), rects scaled as hog.cpp:3527-3532."""
+    if not Ref.available():
+        pytest.skip("oracle/_ref not present")
+    ref = Ref()
+    W, H = 640, 480
+    img = synthetic_frame(4321, W, H, 4, silhouettes=5)
+    det = hog.getDefaultPeopleDetector()
+    rng = np.random.RandomState(9)
+    loc1 = _roi_locations(rng, W, H, 600)
+    _, ec0 = ref.detect_roi(img, det, loc1, hit_threshold=0.0, padding=(8, 8))
+    hit = float(np.percentile(ec0[ec0 != -10.0], 70)) + 0.0123
+    hog.setHitThreshold(hit)
+    for group in (0, 1):
+        er, ec = ref.detect_multiscale_roi(img, det, [(1.0, loc1)], hit_threshold=hit, group_threshold=group)
+        gr, gc = hog.detectMultiScaleROI(img, [(1.0, loc1)], group_threshold=group)
+        assert np.abs(gc[0] - ec[0]).max() <= SCORE_TOL
+        if np.abs(ec[0] - hit).min() > SCORE_TOL:            # no window within tolerance of the threshold: identical sets
+            assert len(er) > 0 and sorted(map(tuple, gr)) == sorted(map(tuple, er))
+    scales = [1.0, 1.05 ** 3, 1.5, 2.0, 2.6]
+    rois, exp_rects = [], []
+    for s in scales:
+        lw, lh = int(np.rint(W / s)), int(np.rint(H / s))
+        loc = _roi_locations(rng, lw, lh, 200)
+        rois.append((s, loc))
+        limg = port.resize(img, lw, lh) if (lw, lh) != (W, H) else img
+        ef, ec = ref.detect_roi(limg, det, loc, hit_threshold=hit, padding=(8, 8))
+        exp_rects.append((ef, ec, s))
+    gr, gc = hog.detectMultiScaleROI(img, rois, group_threshold=0)
+    sure, maybe = [], set()
+    for (ef, ec, s), c, (_, loc) in zip(exp_rects, gc, rois):
+        assert np.abs(c - ec).max() <= SCORE_TOL
+        rect = lambda x, y: (int(np.rint(x * s)), int(np.rint(y * s)), int(np.rint(64 * s)), int(np.rint(128 * s)))
+        for (x, y), e in zip(loc, ec):
+            if e == -10.0:
+                continue
+            if abs(e - hit) <= SCORE_TOL:
+                maybe.add(rect(x, y))                       # within tolerance of the threshold: either answer is right
+            elif e >= hit:
+                sure.append(rect(x, y))
+    got = [tuple(r) for r in gr]
+    assert len(sure) > 0 and [r for r in got if r not in maybe] == [r for r in sure if r not in maybe]   # roi order, location order
+    assert set(got) <= set(sure) | maybe
+    gg, _ = hog.detectMultiScaleROI(img, rois, group_threshold=1)
+    assert np.array_equal(gg, port.group_rectangles(gr, 1))
+    hog.setHitThreshold(0.0)
+
+
 # ------------------------------------------------------------------ groupRectangles on the device (row f4)
 def _rect_cloud(seed, n, nclusters, W=1920, H=1080):
     """Window-like rects (1:2) scattered around cluster centres at several scales, plus isolated ones, in random order."""
