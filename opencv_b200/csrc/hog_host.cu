@@ -136,9 +136,12 @@ struct hogb200 {
     std::vector<float> det_host[kMaxDet];           // as given (column-major blocks + optional bias), for hogb200_save
     // streams
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
-    cudaEvent_t up_done[2] = {nullptr, nullptr}, fr_done[2] = {nullptr, nullptr};
+    // staging slots of the batch path rotate ACROSS calls (a batch never starts on the slot the previous one ended on)
+    static constexpr int kStage = 3;
+    cudaEvent_t up_done[kStage] = {nullptr, nullptr, nullptr}, fr_done[kStage] = {nullptr, nullptr, nullptr};
+    unsigned stage_seq = 0;
     // workspace
-    DevBuf<uint8_t> d_frame[2 * kMaxGroup]; DevBuf<uint8_t> d_raw[2 * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
+    DevBuf<uint8_t> d_frame[kStage * kMaxGroup]; DevBuf<uint8_t> d_raw[kStage * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
     DevBuf<unsigned int> d_queue;   // work-queue counters of the fused histogram kernel (self re-arming)
     int num_sms = 148;
     DevBuf<unsigned char> d_cand;   // [16-byte header: counter][Candidate * cap]
@@ -805,7 +808,7 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->post_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->post_done, cudaEventDisableTiming);
-    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+    for (int i = 0; i < hogb200::kStage && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&h->up_done[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->fr_done[i], cudaEventDisableTiming);
     }
@@ -840,7 +843,7 @@ void hogb200_destroy(hogb200_t* h)
         P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release(); P->d_sitems2.release();
     }
-    for (int i = 0; i < 2; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
+    for (int i = 0; i < hogb200::kStage; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
     for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (BatchJob& J : h->jobs) { J.d_cand.release(); J.h_counts.release(); for (cudaEvent_t e : J.events) cudaEventDestroy(e); }
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
@@ -1160,10 +1163,11 @@ int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, i
     // and the copies (faster than the kernels per frame) stay ahead from then on.
     bool lead_in = false;
     for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
-    lead_in = lead_in && nf > grp && batch_lead_in();
+    // (not when a batch is already in flight: its kernels hide this batch's first uploads)
+    lead_in = lead_in && nf > grp && batch_lead_in() && !h->jobs[0].active && !h->jobs[1].active;
     for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
         ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
-        const int b = gi & 1;                     // double-buffered staging, per group
+        const int b = (int)(h->stage_seq++ % hogb200::kStage);     // staging slots: uploads run up to two groups ahead of the kernels
         FrameRef f[kMaxGroup];
         bool any_host = false;
         for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
