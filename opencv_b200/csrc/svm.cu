@@ -138,18 +138,22 @@ __device__ __forceinline__ void svm_step(float2 (&accA)[kT], float2 (&accB)[kT],
 #pragma unroll
             for (int X = 0; X < kT + C - 1; X++) {
                 const float4 hv = *reinterpret_cast<const float4*>(rowp + X * kHist + 4 * q);
+                // the two halves of the float4 go into the same accumulator: all first halves, then all second halves,
+                // so that the two dependent FFMA2 of an accumulator are up to 14 instructions apart
 #pragma unroll
                 for (int bx = 0; bx < C; bx++) {
                     const int j = X - bx;
                     if (j >= 0 && j < kT) {
-                        if (A) {
-                            accA[j] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), accA[j]);
-                            accA[j] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), accA[j]);
-                        }
-                        if (B) {
-                            accB[j] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), accB[j]);
-                            accB[j] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), accB[j]);
-                        }
+                        if (A) accA[j] = fma2(make_float2(hv.x, hv.y), make_float2(wa[bx].x, wa[bx].y), accA[j]);
+                        if (B) accB[j] = fma2(make_float2(hv.x, hv.y), make_float2(wb[bx].x, wb[bx].y), accB[j]);
+                    }
+                }
+#pragma unroll
+                for (int bx = 0; bx < C; bx++) {
+                    const int j = X - bx;
+                    if (j >= 0 && j < kT) {
+                        if (A) accA[j] = fma2(make_float2(hv.z, hv.w), make_float2(wa[bx].z, wa[bx].w), accA[j]);
+                        if (B) accB[j] = fma2(make_float2(hv.z, hv.w), make_float2(wb[bx].z, wb[bx].w), accB[j]);
                     }
                 }
             }
@@ -187,6 +191,8 @@ __device__ __forceinline__ void svm_step(float2 (&accA)[kT], float2 (&accB)[kT],
 //   empty[slot]  consumers -> producer: all 8 warps are done with the row (a warp also waits for and releases the
 //                rows it does not read)
 template <int C>
+// (9 warps: registers are granted to a CTA in units of 4 warps, so the budget is that of 12 warps -- 168 per thread;
+// __maxnreg__(224) compiles to 215 registers without spills but cannot be launched)
 __global__ void __launch_bounds__(kSvmThreads, 1)
 svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ levels, const SvmItem* __restrict__ items,
            int nitems, const float* __restrict__ hist, const __grid_constant__ SvmParams P, const __grid_constant__ SvmPass S)
