@@ -478,6 +478,9 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     ad[j] = v[j].rbits * (unsigned)kBinBytes + colbase[j];
+#ifdef HOGB200_CHECKS       // tools/build_variant.sh checks -DHOGB200_CHECKS: every vote lands in this warp's own slots, rows 0..9
+                    if (ad[j] < acc0 || ad[j] + kBinBytes + 4 > acc0 + kSlotBytes || (ad[j] - acc0) % 4 != 0) __trap();
+#endif
                     a0[j] = lds32x2<0>(ad[j]); a1[j] = lds32x2<kSlotBytes>(ad[j]); a2[j] = lds32x2<2 * kSlotBytes>(ad[j]);
                 }
 #pragma unroll

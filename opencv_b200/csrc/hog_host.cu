@@ -333,7 +333,7 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
             L.img_off = pyr; pyr += align_up((size_t)L.pitch * L.h, 256);
             D.xtab_off = (int)xtab.size(); D.ytab_off = (int)ytab.size();
             if (L.mode == 1) { resize_table(W, L.w, true, xtab); resize_table(H, L.h, false, ytab); }
-            if (L.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(&xtab[D.xtab_off], L.w, &ytab[D.ytab_off], L.h, W);
+            if (L.mode == 1) D.rs_rows = resize_plan_rows(&xtab[D.xtab_off], L.w, &ytab[D.ytab_off], L.h, W, cn);
             const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
             for (int y = 0; y < L.h; y += th)
                 for (int x = 0; x < L.w; x += tw) ritems.push_back(ResizeItem{(short)i, (short)x, (short)y, 0});
@@ -1542,7 +1542,7 @@ int hogb200_resize(hogb200_t* h, const hogb200_image* img, int dst_w, int dst_h,
     D.mode = is_exact_half(W, H, dst_w, dst_h) ? 2 : 1;
     std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
     if (D.mode == 1) { resize_table(W, dst_w, true, xt); resize_table(H, dst_h, false, yt); }
-    if (D.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(xt.data(), dst_w, yt.data(), dst_h, W);
+    if (D.mode == 1) D.rs_rows = resize_plan_rows(xt.data(), dst_w, yt.data(), dst_h, W, cn);
     const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
     for (int y = 0; y < dst_h; y += th) for (int x = 0; x < dst_w; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
     DevBuf<uint8_t> d_out; DevBuf<LevelDesc> d_lv; DevBuf<ResizeCoef> d_xt, d_yt; DevBuf<ResizeItem> d_it;
@@ -1605,7 +1605,7 @@ int roi_level_image(hogb200* h, const FrameRef& f, int W, int H, int cn, int dw,
     D.mode = is_exact_half(W, H, dw, dh) ? 2 : 1;
     std::vector<ResizeCoef> xt, yt; std::vector<ResizeItem> items;
     if (D.mode == 1) { resize_table(W, dw, true, xt); resize_table(H, dh, false, yt); }
-    if (D.mode == 1 && cn == 4) D.rs_rows = resize_plan_rows(xt.data(), dw, yt.data(), dh, W);
+    if (D.mode == 1) D.rs_rows = resize_plan_rows(xt.data(), dw, yt.data(), dh, W, cn);
     const int tw = resize_tile_w(cn), th = resize_tile_h(cn, D.rs_rows);
     for (int y = 0; y < dh; y += th) for (int x = 0; x < dw; x += tw) items.push_back(ResizeItem{0, (short)x, (short)y, 0});
     CK(cudaStreamSynchronize(st));          // the tables below are freed at the end of this call: nothing may still read older ones

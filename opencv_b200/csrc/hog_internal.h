@@ -42,7 +42,7 @@ struct LevelDesc {
     long long score_off;  // float offset of this level's [nwy][nwx] plane in the score buffer
     int xtab_off, ytab_off;  // offsets into the resize coefficient tables (entries)
     int mode;             // 0 = alias/copy of base, 1 = bilinear, 2 = exact-2x area
-    int rs_rows;          // 8UC4 resize: destination rows per warp and staging scheme (resize_plan_rows)
+    int rs_rows;          // resize: destination rows per warp and staging scheme (resize_plan_rows)
 };
 
 // resize coefficient table entry (one per destination column / row of a level), everything the kernel would
@@ -71,7 +71,7 @@ struct Candidate { int level; int x; int y; float score; };
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------------
 int resize_tile_w(int cn);   // tile geometry the host uses to build ResizeItems
 int resize_tile_h(int cn, int rs_rows);
-int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w);
+int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w, int cn);
 // 8UC3 (B,G,R) -> 8UC4 (B,G,R,255): the colour conversion example_gpu_tbd does on the host before the upload
 // (samples/gpu/tbd.cpp:573-599), moved to the device.  dst rows are 16-byte aligned.
 void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st);

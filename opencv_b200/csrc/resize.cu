@@ -266,6 +266,9 @@ resize_c4_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
             bulk_g2s(tile + off1, src0 + (size_t)cyl.s1 * bpitch, rowbytes, mbar);
         }
         mbar_wait(mbar, ch & 1);
+#ifdef HOGB200_CHECKS       // the staged rows fit the warp's slice (resize_plan_rows promised it)
+        if (nstaged * rowbytes + 16 > (unsigned)kRsWarpBytes) __trap();
+#endif
 
         unsigned r1 = 0xffffffffu;
         bool par = false;           // false: lower tap of the previous row is in B; true: in A
@@ -349,51 +352,175 @@ resize_c4_direct_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __
     direct_rows(base, bpitch, cxa, cxb, yt, nrows, dst, dpitch, va, vb);
 }
 
-// 8UC1: one thread = four consecutive destination pixels (one 4-byte store); tile 128 x 8.
-__global__ void __launch_bounds__(256)
+// 8UC1.  A warp owns 128 columns x R rows of a level (lane <-> 4 adjacent destination pixels, one 4-byte store per row)
+// and walks DOWN the rows, kRsChunks chunks of R rows.  The source rows of a chunk are staged in the warp's private slice
+// of shared memory with 32-bit loads (an 8UC1 frame only promises 4-byte aligned rows, which rules the 16-byte bulk copy
+// out); from there the two taps of a pixel are two aligned 32-bit shared loads + one PRMT that picks bytes (sx, sx + 1)
+// -- never a byte load -- and one IDP.2A; the horizontal pass of a source row is reused by the next destination row when
+// it needs the same row; the vertical pass is two multiplies per pixel whose upper halves are packed pairwise by PRMT,
+// rounded and shifted together and assembled into the 4 output bytes by a last PRMT (resize.cpp:1491-1542, 1577-1603).
+constexpr int kR1TileW = 128;
+
+struct HRow1 { int t[4]; };      // horizontal result >> 4 of the lane's four pixels
+
+__device__ __forceinline__ HRow1 hrow1_smem(unsigned rowaddr, const unsigned (&woff)[4], const unsigned (&sel)[4], const unsigned (&a01)[4])
+{
+    HRow1 h;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        unsigned w0, w1;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(rowaddr + woff[k]));
+        asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(w1) : "r"(rowaddr + woff[k]));
+        const unsigned pair = __byte_perm(w0, w1, sel[k]);            // (S[sx], S[sx+1], 0, 0)
+        h.t[k] = (int)(__dp2a_lo(a01[k], pair, 0u) >> 4);             // (S[sx]*a0 + S[sx+1]*a1) >> 4
+    }
+    return h;
+}
+__device__ __forceinline__ unsigned vertical_pack1(const HRow1& h0, const HRow1& h1, unsigned b0, unsigned b1)
+{
+    const unsigned x0 = b0 * (unsigned)h0.t[0], x1 = b0 * (unsigned)h0.t[1], x2 = b0 * (unsigned)h0.t[2], x3 = b0 * (unsigned)h0.t[3];
+    const unsigned y0 = b1 * (unsigned)h1.t[0], y1 = b1 * (unsigned)h1.t[1], y2 = b1 * (unsigned)h1.t[2], y3 = b1 * (unsigned)h1.t[3];
+    const unsigned p01 = __byte_perm(x0, x1, 0x7632) + __byte_perm(y0, y1, 0x7632) + 0x00020002u;
+    const unsigned p23 = __byte_perm(x2, x3, 0x7632) + __byte_perm(y2, y3, 0x7632) + 0x00020002u;
+    return __byte_perm(p01 >> 2, p23 >> 2, 0x6420);
+}
+
+__global__ void __launch_bounds__(kRsWarps * 32)
 resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
                  const LevelDesc* __restrict__ levels, const ResizeCoef* __restrict__ xtab,
                  const ResizeCoef* __restrict__ ytab, const ResizeItem* __restrict__ items)
 {
+    extern __shared__ __align__(16) unsigned char rs_smem[];
     const ResizeItem it = items[blockIdx.x];
     if (it.frame >= fs.nframes) return;
     const uint8_t* __restrict__ base = fs.base[it.frame];
     const int bpitch = fs.pitch[it.frame];
     const LevelDesc& L = levels[it.level];
-    const int x4 = it.x0 + 4 * (threadIdx.x & 31), y = it.y0 + (threadIdx.x >> 5);
-    if (x4 >= L.w || y >= L.h) return;
-    uint8_t o[4] = {0, 0, 0, 0};
-    if (L.mode == 2) {
-        const uint8_t* r0 = base + (size_t)(2 * y) * bpitch;
-        const uint8_t* r1 = r0 + bpitch;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int w = L.w, h = L.h, rs = L.rs_rows;
+    const int R = rs > 0 ? rs : (rs < 0 ? -rs : kRsDirectRows);
+    const int RW = rs != 0 ? R * kRsChunks : R;              // rows of this warp
+    const int y0 = it.y0 + warp * RW;
+    if (y0 >= h) return;                                     // the whole warp
+    const int nrows = min(RW, h - y0);
+    const int x4 = it.x0 + 4 * lane;
+    const int dpitch = L.pitch;
+    uint8_t* __restrict__ dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y0 * dpitch + x4;
+    const bool full = x4 + 3 < w;                            // level pitch is a multiple of 64: a whole-word store is in bounds
+
+    if (L.mode == 2 || rs == 0) {
+        // exact half (2x2 box average, resize.cpp:2542-2578) and levels too coarse to stage (a handful of small ones): per-pixel loads
+        const ResizeCoef* __restrict__ xt = xtab + L.xtab_off;
+        for (int k = 0; k < nrows; k++, dst += dpitch) {
+            const int y = y0 + k;
+            uint8_t o[4] = {0, 0, 0, 0};
+            if (L.mode == 2) {
+                const uint8_t* r0 = base + (size_t)(2 * y) * bpitch;
+                const uint8_t* r1 = r0 + bpitch;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int x = x4 + k;
-            if (x < L.w) o[k] = (__ldg(r0 + 2 * x) + __ldg(r0 + 2 * x + 1) + __ldg(r1 + 2 * x) + __ldg(r1 + 2 * x + 1) + 2) >> 2;
+                for (int j = 0; j < 4; j++) {
+                    const int x = x4 + j;
+                    if (x < w) o[j] = (__ldg(r0 + 2 * x) + __ldg(r0 + 2 * x + 1) + __ldg(r1 + 2 * x) + __ldg(r1 + 2 * x + 1) + 2) >> 2;
+                }
+            } else {
+                const ResizeCoef cy = ytab[L.ytab_off + y];
+                const int b0 = (int)cy.c0, b1 = (int)cy.c1;
+                const uint8_t* r0 = base + (size_t)cy.s0 * bpitch;
+                const uint8_t* r1 = base + (size_t)cy.s1 * bpitch;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int x = x4 + j;
+                    if (x < w) {
+                        const ResizeCoef cx = xt[x];
+                        const int a0 = (int)(cx.c0 & 0xffffu), a1 = (int)(cx.c0 >> 16);
+                        o[j] = vlin(__ldg(r0 + cx.s0) * a0 + __ldg(r0 + cx.s1) * a1, __ldg(r1 + cx.s0) * a0 + __ldg(r1 + cx.s1) * a1, b0, b1);
+                    }
+                }
+            }
+            if (full) *reinterpret_cast<uchar4*>(dst) = make_uchar4(o[0], o[1], o[2], o[3]);
+            else for (int j = 0; j < 4 && x4 + j < w; j++) dst[j] = o[j];
         }
-    } else {
-        const ResizeCoef cy = ytab[L.ytab_off + y];
-        const int sy0 = cy.s0, sy1 = cy.s1;
-        const int b0 = (int)cy.c0, b1 = (int)cy.c1;
-        const uint8_t* r0 = base + (size_t)sy0 * bpitch;
-        const uint8_t* r1 = base + (size_t)sy1 * bpitch;
+        return;
+    }
+    const ResizeCoef* __restrict__ xt = xtab + L.xtab_off;
+    const ResizeCoef* __restrict__ yt = ytab + L.ytab_off + y0;
+
+    // ---- the warp's slice: [row table 16 B x R][staged source bytes]
+    const unsigned ws = (unsigned)__cvta_generic_to_shared(rs_smem) + warp * kRsWarpStride;
+    const unsigned ycoef = ws + 16, tile = ws + kRsHeader;
+    const int c_lo = xt[it.x0].s0 & ~3;                                    // first staged source column
+    int span = (xt[min(it.x0 + kR1TileW, w) - 1].s0 + 2 - c_lo + 3) & ~3; // through the second tap of the last column
+    span = min(span, ((bw + 3) & ~3) - c_lo);                              // rows are readable up to the next multiple of 4
+    const unsigned rowbytes = (unsigned)span, rowwords = rowbytes >> 2;
+    const uint8_t* __restrict__ src0 = base + c_lo;
+    unsigned woff[4], sel[4], a01[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int x = x4 + k;
-            if (x < L.w) {
-                const ResizeCoef cx = xtab[L.xtab_off + x];
-                const int sx0 = cx.s0, sx1 = cx.s1;
-                const int a0 = (int)(cx.c0 & 0xffffu), a1 = (int)(cx.c0 >> 16);
-                o[k] = vlin(__ldg(r0 + sx0) * a0 + __ldg(r0 + sx1) * a1,
-                            __ldg(r1 + sx0) * a0 + __ldg(r1 + sx1) * a1, b0, b1);
+    for (int k = 0; k < 4; k++) {
+        const ResizeCoef c = xt[min(x4 + k, w - 1)];
+        const unsigned off = (unsigned)(c.s0 - c_lo);
+        woff[k] = off & ~3u;
+        sel[k] = 0x4400u | (off & 3u) | (((off & 3u) + 1u) << 4);          // bytes off, off + 1 of the word pair; upper half zero
+        a01[k] = c.c0;
+    }
+    HRow1 A, B;
+#pragma unroll
+    for (int k = 0; k < 4; k++) A.t[k] = B.t[k] = 0;
+    for (int k0 = 0; k0 < nrows; k0 += R, yt += R) {
+        const int nr = min(R, nrows - k0);                  // destination rows of this chunk
+        const ResizeCoef cyl = yt[min(lane, nr - 1)];
+        const int r_lo = __shfl_sync(0xffffffffu, cyl.s0, 0);
+        const int r_hi = __shfl_sync(0xffffffffu, cyl.s1, nr - 1);
+        const int nstaged = rs > 0 ? r_hi - r_lo + 1 : 2 * nr;
+        const unsigned off0 = rs > 0 ? (cyl.s0 - r_lo) * rowbytes : 2 * lane * rowbytes;
+        const unsigned off1 = rs > 0 ? (cyl.s1 - r_lo) * rowbytes : off0 + rowbytes;
+        __syncwarp();                                       // every lane is done with the previous chunk's slice and row table
+        if (lane < nr)
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(ycoef + 16 * lane), "r"(off0), "r"(off1), "r"(cyl.c0), "r"(cyl.c1) : "memory");
+        // stage: word i of staged row j; the source row of staged row j is r_lo + j, or the j-th of the (s0, s1) pairs
+        const int total = nstaged * (int)rowwords;
+#ifdef HOGB200_CHECKS
+        if (nstaged * rowbytes + 16 > (unsigned)kRsWarpBytes) __trap();
+#endif
+        for (int i0 = 0; i0 < total; i0 += 128) {           // four words in flight per lane
+            unsigned v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + 32 * u + lane;
+                if (i < total) {
+                    const int j = i / (int)rowwords, wd = i - j * (int)rowwords;
+                    int srow = r_lo + j;
+                    if (rs < 0) { const ResizeCoef cj = yt[j >> 1]; srow = (j & 1) ? cj.s1 : cj.s0; }
+                    v[u] = __ldg(reinterpret_cast<const unsigned*>(src0 + (size_t)srow * bpitch) + wd);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + 32 * u + lane;
+                if (i < total) asm volatile("st.shared.u32 [%0], %1;" ::"r"(tile + 4 * i), "r"(v[u]) : "memory");
             }
         }
-    }
-    uint8_t* dst = const_cast<uint8_t*>(L.img) + it.frame * fs.pyr_stride + (size_t)y * L.pitch + x4;
-    if (x4 + 3 < L.w) {
-        *reinterpret_cast<uchar4*>(dst) = make_uchar4(o[0], o[1], o[2], o[3]);   // level pitch is a multiple of 16
-    } else {
-        for (int k = 0; k < 4 && x4 + k < L.w; k++) dst[k] = o[k];
+        __syncwarp();
+
+        unsigned r1 = 0xffffffffu;
+        bool par = false;           // false: lower tap of the previous row is in B; true: in A
+        for (int k = 0; k < nr; k++, dst += dpitch) {
+            unsigned o0, o1, b0, b1;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(o0), "=r"(o1), "=r"(b0), "=r"(b1) : "r"(ycoef + 16 * k));
+            unsigned out;
+            if (o0 == r1) {
+                if (par) { B = hrow1_smem(tile + o1, woff, sel, a01); out = vertical_pack1(A, B, b0, b1); }
+                else     { A = hrow1_smem(tile + o1, woff, sel, a01); out = vertical_pack1(B, A, b0, b1); }
+                par = !par;
+            } else {
+                A = hrow1_smem(tile + o0, woff, sel, a01);
+                B = hrow1_smem(tile + o1, woff, sel, a01);
+                out = vertical_pack1(A, B, b0, b1);
+                par = false;
+            }
+            r1 = o1;
+            if (full) *reinterpret_cast<unsigned*>(dst) = out;
+            else for (int j = 0; j < 4 && x4 + j < w; j++) dst[j] = (uint8_t)(out >> (8 * j));
+        }
     }
 }
 
@@ -469,24 +596,24 @@ bool resize_direct()
 int resize_tile_w(int cn) { return cn == 4 ? kRsTileW : 128; }
 int resize_tile_h(int cn, int rs_rows)
 {
-    if (cn != 4) return 8;
-    if (resize_direct()) return kRdWarps * kRdRows;
+    if (cn == 4 && resize_direct()) return kRdWarps * kRdRows;
     return kRsWarps * (rs_rows > 0 ? rs_rows * kRsChunks : (rs_rows < 0 ? -rs_rows * kRsChunks : kRsDirectRows));
 }
 
 // Destination rows per warp for one 8UC4 level, from the level's own coefficient tables: the largest R whose
 // staged source slice fits kRsWarpBytes for every warp tile.  > 0: the rows [s0(first), s1(last)] are staged as
 // one range; < 0: only the two source rows of every destination row (cheaper from scale 2 up); 0: no staging.
-int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w)
+int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int dst_h, int src_w, int cn)
 {
+    const int tile_w = cn == 4 ? kRsTileW : kR1TileW;
     int span = 0;
-    for (int x0 = 0; x0 < dst_w; x0 += kRsTileW) {
+    for (int x0 = 0; x0 < dst_w; x0 += tile_w) {
         const int c_lo = xt[x0].s0 & ~3;
-        int sp = (xt[std::min(x0 + kRsTileW, dst_w) - 1].s0 + 2 - c_lo + 3) & ~3;
+        int sp = (xt[std::min(x0 + tile_w, dst_w) - 1].s0 + 2 - c_lo + 3) & ~3;
         sp = std::min(sp, ((src_w + 3) & ~3) - c_lo);
         span = std::max(span, sp);
     }
-    const int rowbytes = 4 * span, slack = 16;      // the second tap of the last column may lie one pixel past the span
+    const int rowbytes = cn * span, slack = 16;     // the second tap of the last column may lie one pixel past the span
     // staging pays only when the per-warp setup (mbarrier, one bulk copy per source row) is spread over enough rows
     static const int min_rows = [] { const char* e = getenv("HOGB200_RS_MINROWS"); return e ? atoi(e) : 8; }();
     for (int R = kRsMaxRows; R >= std::max(1, min_rows); R >>= 1) {
@@ -512,8 +639,10 @@ void launch_resize(const FrameSet& fs, int bw, int bh, int cn,
         if (smem > 48 * 1024) cudaFuncSetAttribute(resize_c4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         resize_c4_kernel<<<nitems, kRsWarps * 32, smem, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
     }
-    else
-        resize_c1_kernel<<<nitems, 256, 0, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+    else {
+        constexpr int smem = kRsWarps * kRsWarpStride + 16;
+        resize_c1_kernel<<<nitems, kRsWarps * 32, smem, st>>>(fs, bw, bh, d_levels, d_xtab, d_ytab, d_items);
+    }
 }
 
 }  // namespace hogk

@@ -324,6 +324,10 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
             // poll the next step's row now, so that the answer is there when this step's arithmetic is done
             ready = t == win_by || mbar_test(full0 + 8 * nslot, npar);
             const float* rowp = ringp + slot_l * kRowFloats + cg * kT * kHist;
+#ifdef HOGB200_CHECKS       // the row this lane reads is inside the ring, and the producer has declared it full
+            if (slot_l >= (unsigned)ring || (cg * kT + kT + wbxp - 1) * kHist > kRowFloats ||
+                !mbar_test(full0 + 8 * slot_l, ((pos0 + 2 * pr + t) / ring) & 1)) __trap();
+#endif
             const float* ca = mycoef + t * crow;
             const float* cb = ca - crow;
             if (t == 0) svm_step<C, true, false>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);

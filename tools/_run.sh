@@ -1,3 +1,5 @@
-HOGB200_TRACE=1 python tools/trace_batch.py 2> gpurun_out/r02d_trace.txt; tail -12 gpurun_out/r02d_trace.txt
-sed -i 's/r02a_prof_/r02d_prof_/' tools/prof_three_kernels.sh
-bash tools/prof_three_kernels.sh 2>&1 | tail -3
+python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+echo "== checks variant (device-side bounds traps)"; HOGB200_LIB=build_variants/libhogb200_checks.so python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python tools/race_repeat.py 25 2>&1 | tee gpurun_out/r02_race_repeat.txt
+python tools/prof_batch.py 6
+python bench.py --workload vga --quick --no-cpu --steps 10 --warmup 3 | cut -c1-1400

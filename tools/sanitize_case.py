@@ -38,4 +38,17 @@ hog.setWinStride((64, 128)); d = hog.compute(img); hog.setWinStride((8, 8))
 print("compute:", d.shape)
 r = np.stack([np.arange(4000) % 97 * 8, np.arange(4000) % 53 * 8, np.full(4000, 64), np.full(4000, 128)], 1).astype(np.int32)
 print("device groupRectangles:", len(hog.groupRectanglesDevice(r, 2, 0.2)))
+import torch  # noqa: E402
+t0 = hog.submitBatch(frames[:3], nslots=2); t1 = hog.submitBatch(gray[:4])
+print("submit/collect:", sum(len(o) for o in hog.collectBatch(t1)), sum(len(o) for o in hog.collectBatch(t0)), "rects")
+os.environ["HOGB200_GPU_POST_MIN"] = "1"
+print("device tail:", sum(len(o) for o in hog.detectMultiScaleBatch(frames[:3], nslots=2)), "rects")
+os.environ.pop("HOGB200_GPU_POST_MIN")
+loc = np.stack([np.arange(-1, 30) * 8, np.arange(-1, 30) % 7 * 8], 1).astype(np.int32)
+print("detectROI:", len(hog.detectROI(img, loc)[0]), "hits;", len(hog.detectMultiScaleROI(img, [(1.0, loc), (1.3, loc)], 1)[0]), "grouped")
+d_img = torch.from_numpy(img).cuda(); out = torch.zeros((31, 39, 36), dtype=torch.float32, device="cuda")
+hog.blockHistogramsNoAlloc(d_img, out); torch.cuda.synchronize()
+print("no-alloc histograms:", float(out.abs().sum()) > 0)
+wide = HOG.create(win_size=(128, 64)); wide.setSVMDetector((np.random.RandomState(2).randn(15 * 7 * 36 + 1) * 0.05).astype(np.float32))
+print("128x64 window:", wide.windowScores(frames[0]).shape)
 print("sanitize_case ok")
