@@ -62,8 +62,18 @@ constexpr int kStgBytes = kTileBlocks * kHist * 4; // 2016 B: the normalisation 
 constexpr float kMagic = 8388624.f;                // 2^23 + 16: q + kMagic has ulp 1 for q in [-4.5, 4.5], mantissa = 16 + n
 static_assert(kStgBytes <= kSlotBytes && kStgBytes % 16 == 0 && kSlotBytes % 16 == 0, "staging plane must fit a slot");
 
+// HOGB200_HIST_BULK=1 (measurement variant, tools/build_variant.sh): the rows of a tile reach the warp through a ring of
+// cp.async.bulk copies into shared memory (the TMA-staged form north_star (2) prescribes) instead of one LDG.128 per
+// lane and row.  8UC4 only; needs HOGB200_LUT_COPIES=16 to make room for the rings.  DESIGN.md 4.1 has both timings.
+#ifndef HOGB200_HIST_BULK
+#define HOGB200_HIST_BULK 0
+#endif
 struct __align__(16) WarpSmem {
     float acc[3][kRows][4][kVote];                 // 15,360 B  vertical partial sums
+#if HOGB200_HIST_BULK
+    unsigned char ring[kPF][512];                  //  2,048 B  staged rows: 32 lanes x 16 B
+    unsigned long long bar[kPF];                   //     32 B  one mbarrier per ring slot
+#endif
 };
 struct __align__(16) Smem {
     float4 wrow[3][8];                             //    384 B  vertical weights of row o of a cell row, per slot, for the
@@ -160,6 +170,29 @@ __device__ __forceinline__ float rcp_approx(float x)
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+
+#if HOGB200_HIST_BULK
+__device__ __forceinline__ void hb_init(unsigned mbar)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar));
+}
+__device__ __forceinline__ void hb_issue(unsigned dst, const void* src, unsigned bytes, unsigned mbar)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void hb_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "HBW_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra HBD_%=;\n\t"
+        "bra HBW_%=;\n\t"
+        "HBD_%=:\n\t}" ::"r"(mbar), "r"(parity), "r"(0x989680u) : "memory");
+}
+#endif
 
 template <int CN> struct RawT { typedef uint4 T; };
 template <> struct RawT<1> { typedef unsigned int T; };
@@ -381,7 +414,7 @@ __device__ __forceinline__ void normalize_store(unsigned stg, int lane, int nblk
 template <int CN>
 __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistItem it, const LevelDesc& L,
                                              const FrameSet& fs, const BlockWeights& W,
-                                             float l2hys, float* __restrict__ hist_all, int lane)
+                                             float l2hys, float* __restrict__ hist_all, int lane, unsigned& bulk_seq)
 {
     const int frame = it.level >> 8;
     const uint8_t* __restrict__ base = fs.base[frame];
@@ -394,6 +427,13 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
     const int xt = it.bx0 * kCell - 4 + 4 * lane;           // first of this lane's 4 columns (lane 0 / 31: halo)
     const int chunk = min(max(xt >> 2, 0), (w - 1) >> 2);   // clamped: out-of-range columns never reach an output
     const uint8_t* __restrict__ colp = img + (size_t)chunk * kChunk;
+#if HOGB200_HIST_BULK
+    // the 16-byte chunks the 32 lanes read are one contiguous (clamped) segment of the row: lane 0's chunk .. lane 31's
+    const int c_first = min(max((it.bx0 * kCell - 4) >> 2, 0), (w - 1) >> 2), c_last = min(max((it.bx0 * kCell - 4 + 124) >> 2, 0), (w - 1) >> 2);
+    const uint8_t* __restrict__ segp = img + (size_t)c_first * kChunk;
+    const unsigned seg_bytes = (unsigned)(c_last - c_first + 1) * 16u, lane_seg = (unsigned)(chunk - c_first) * 16u;
+    const unsigned ring0 = (unsigned)__cvta_generic_to_shared(&ws.ring[0][0]), bar0 = (unsigned)__cvta_generic_to_shared(&ws.bar[0]);
+#endif
     float xm[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) xm[j] = (xt + j <= 0 || xt + j >= w - 1) ? 0.f : 1.f;
@@ -434,6 +474,10 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
 #pragma unroll
         for (int k = 0; k < kPF; k++) {
             const int yy = y + 1 + k;
+#if HOGB200_HIST_BULK
+            if (CN == 4) { if (lane == 0) hb_issue(ring0 + 512 * ((bulk_seq + k) % kPF), segp + (size_t)(yy >= h ? h - 2 : yy) * pitch, seg_bytes, bar0 + 8 * ((bulk_seq + k) % kPF)); }
+            else
+#endif
             pf[k] = load_raw<CN>(colp + (size_t)(yy >= h ? h - 2 : yy) * pitch);
         }
     }
@@ -451,8 +495,22 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
 #pragma unroll
             for (int k = 0; k < 4; k++, y++) {
                 // row y+1 (reflect-101 at the bottom: dy = 0 on the last row), and the prefetch kPF rows ahead
-                unpack<CN>(pf[k % kPF], sel, lutl, D);
+#if HOGB200_HIST_BULK
+                if (CN == 4) {
+                    const unsigned slot = bulk_seq % kPF;
+                    hb_wait(bar0 + 8 * slot, (bulk_seq / kPF) & 1);
+                    uint4 raw;
+                    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w) : "r"(ring0 + 512 * slot + lane_seg));
+                    pf[0] = *reinterpret_cast<typename RawT<CN>::T*>(&raw);
+                    __syncwarp();                               // every lane has its chunk: the slot may be refilled
+                    const int yy = y + 1 + kPF;
+                    if (lane == 0) hb_issue(ring0 + 512 * slot, segp + (size_t)(yy >= h ? h - 2 : yy) * pitch, seg_bytes, bar0 + 8 * slot);
+                    bulk_seq++;
+                    unpack<CN>(pf[0], sel, lutl, D);
+                } else
+#endif
                 {
+                    unpack<CN>(pf[k % kPF], sel, lutl, D);
                     const int yy = y + 1 + kPF;
                     pf[k % kPF] = load_raw<CN>(colp + (size_t)(yy >= h ? h - 2 : yy) * pitch);
                 }
@@ -519,6 +577,12 @@ __device__ __forceinline__ void process_item(Smem& s, WarpSmem& ws, const HistIt
         rot = rot == 2 ? 0 : rot + 1;
         slot_p = slot_p == 0 ? 2 : slot_p - 1;
     }
+#if HOGB200_HIST_BULK
+    if (CN == 4) {              // the rows prefetched past the strip: wait them out so that slot phases stay in step
+        for (int k = 0; k < kPF; k++, bulk_seq++) hb_wait(bar0 + 8 * (bulk_seq % kPF), (bulk_seq / kPF) & 1);
+        __syncwarp();
+    }
+#endif
 }
 
 template <int CN>
@@ -559,6 +623,13 @@ hist_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ l
     __syncthreads();
 
     WarpSmem& ws = s.w[warp];
+    unsigned bulk_seq = 0;          // rows this warp has pushed through its ring (HOGB200_HIST_BULK)
+#if HOGB200_HIST_BULK
+    if (lane == 0)
+        for (int i = 0; i < kPF; i++) hb_init((unsigned)__cvta_generic_to_shared(&ws.bar[i]));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+#endif
     // work queue, one item ahead: the next index and descriptor are in flight while the current item is processed
     auto fetch = [&]() {
         int i = 0;
@@ -571,7 +642,7 @@ hist_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ l
         const int nidx = fetch();
         const HistItem nit = items[min(nidx, nitems - 1)];
         if ((it.level >> 8) < fs.nframes)       // items of absent frames (partial group) are skipped
-            process_item<CN>(s, ws, it, levels[it.level & 255], fs, W, l2hys, hist, lane);
+            process_item<CN>(s, ws, it, levels[it.level & 255], fs, W, l2hys, hist, lane, bulk_seq);
         idx = nidx; it = nit;
     }
     // the last worker to run dry re-arms the queue for the next launch on this stream

@@ -1,5 +1,4 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-echo "== checks variant (device-side bounds traps)"; HOGB200_LIB=build_variants/libhogb200_checks.so python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-python tools/race_repeat.py 25 2>&1 | tee gpurun_out/r02_race_repeat.txt
-python tools/prof_batch.py 6
-python bench.py --workload vga --quick --no-cpu --steps 10 --warmup 3 | cut -c1-1400
+baseline/_ref/ref_cuda_bench 2>&1 | tee gpurun_out/r02_ref_cuda_kernels.txt
+echo "--- ours, same GPU: one 1080p frame per launch (all 44 levels in 3 launches), then 4 frames per launch" | tee -a gpurun_out/r02_ref_cuda_kernels.txt
+python tools/prof_one.py 6 2>&1 | tee -a gpurun_out/r02_ref_cuda_kernels.txt
+python tools/prof_batch.py 6 2>&1 | tee -a gpurun_out/r02_ref_cuda_kernels.txt
