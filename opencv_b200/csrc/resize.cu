@@ -360,6 +360,11 @@ resize_c4_direct_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __
 // it needs the same row; the vertical pass is two multiplies per pixel whose upper halves are packed pairwise by PRMT,
 // rounded and shifted together and assembled into the 4 output bytes by a last PRMT (resize.cpp:1491-1542, 1577-1603).
 constexpr int kR1TileW = 128;
+#ifndef HOGB200_R1_CHUNKS
+#define HOGB200_R1_CHUNKS 1
+#endif
+constexpr int kR1Chunks = HOGB200_R1_CHUNKS;       // chunks of R rows per warp: 8UC1 pyramids are small (VGA: 3 Mpx), a 128 x 256 tile
+                                                    // (4 chunks) leaves the SMs a handful of CTAs each
 
 struct HRow1 { int t[4]; };      // horizontal result >> 4 of the lane's four pixels
 
@@ -399,7 +404,7 @@ resize_c1_kernel(const __grid_constant__ FrameSet fs, int bw, int bh,
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int w = L.w, h = L.h, rs = L.rs_rows;
     const int R = rs > 0 ? rs : (rs < 0 ? -rs : kRsDirectRows);
-    const int RW = rs != 0 ? R * kRsChunks : R;              // rows of this warp
+    const int RW = rs != 0 ? R * kR1Chunks : R;              // rows of this warp
     const int y0 = it.y0 + warp * RW;
     if (y0 >= h) return;                                     // the whole warp
     const int nrows = min(RW, h - y0);
@@ -597,7 +602,8 @@ int resize_tile_w(int cn) { return cn == 4 ? kRsTileW : 128; }
 int resize_tile_h(int cn, int rs_rows)
 {
     if (cn == 4 && resize_direct()) return kRdWarps * kRdRows;
-    return kRsWarps * (rs_rows > 0 ? rs_rows * kRsChunks : (rs_rows < 0 ? -rs_rows * kRsChunks : kRsDirectRows));
+    const int chunks = cn == 4 ? kRsChunks : kR1Chunks;
+    return kRsWarps * (rs_rows > 0 ? rs_rows * chunks : (rs_rows < 0 ? -rs_rows * chunks : kRsDirectRows));
 }
 
 // Destination rows per warp for one 8UC4 level, from the level's own coefficient tables: the largest R whose
@@ -616,7 +622,8 @@ int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int 
     const int rowbytes = cn * span, slack = 16;     // the second tap of the last column may lie one pixel past the span
     // staging pays only when the per-warp setup (mbarrier, one bulk copy per source row) is spread over enough rows
     static const int min_rows = [] { const char* e = getenv("HOGB200_RS_MINROWS"); return e ? atoi(e) : 8; }();
-    for (int R = kRsMaxRows; R >= std::max(1, min_rows); R >>= 1) {
+    // (8UC1 stages with plain loads, no per-warp barrier set-up: any R pays, and the unstaged path costs eight byte loads per pixel)
+    for (int R = kRsMaxRows; R >= (cn == 1 ? 1 : std::max(1, min_rows)); R >>= 1) {
         int range = 0;
         for (int y0 = 0; y0 < dst_h; y0 += R)
             range = std::max(range, yt[std::min(y0 + R, dst_h) - 1].s1 - yt[y0].s0 + 1);

@@ -121,13 +121,14 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
 // the upper window row of the pair (accA) and cb for the lower one (accB); A / B say which of the two window rows
 // contain this block row (the first step has no B, the last no A).  The window's columns come in `nchunks` chunks
 // of C blocks: chunk c of the coefficients meets the histograms C * c blocks further right.
-template <int C, bool A, bool B>
+template <int C, bool MULTI, bool A, bool B>
 __device__ __forceinline__ void svm_step(float2 (&accA)[kT], float2 (&accB)[kT], float2 (&exA)[2], float2 (&exB)[2],
                                          const float* __restrict__ ca, const float* __restrict__ cb,
                                          const float* __restrict__ rowp, int q, int nchunks)
 {
+    // MULTI = false: windows of at most 8 block columns (64x128, 48x96, ...) are one chunk -- straight-line code
 #pragma unroll 1
-    for (int ch = 0; ch < nchunks; ch++, ca += C * kHist, cb += C * kHist, rowp += C * kHist) {
+    for (int ch = 0; ch < (MULTI ? nchunks : 1); ch++, ca += C * kHist, cb += C * kHist, rowp += C * kHist) {
         {   // float4 number q of every block, all 16 windows
             float4 wa[C], wb[C];
 #pragma unroll
@@ -190,7 +191,7 @@ __device__ __forceinline__ void svm_step(float2 (&accA)[kT], float2 (&accB)[kT],
 //   full[slot]   producer -> consumers: the row's bytes have landed (expect_tx / complete_tx)
 //   empty[slot]  consumers -> producer: all 8 warps are done with the row (a warp also waits for and releases the
 //                rows it does not read)
-template <int C>
+template <int C, bool MULTI>
 // (9 warps: registers are granted to a CTA in units of 4 warps, so the budget is that of 12 warps -- 168 per thread;
 // __maxnreg__(224) compiles to 215 registers without spills but cannot be launched)
 __global__ void __launch_bounds__(kSvmThreads, 1)
@@ -330,9 +331,9 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
 #endif
             const float* ca = mycoef + t * crow;
             const float* cb = ca - crow;
-            if (t == 0) svm_step<C, true, false>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
-            else if (t == win_by) svm_step<C, false, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
-            else svm_step<C, true, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            if (t == 0) svm_step<C, MULTI, true, false>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            else if (t == win_by) svm_step<C, MULTI, false, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
+            else svm_step<C, MULTI, true, true>(accA, accB, exA, exB, ca, cb, rowp, q, S.nchunks);
             __syncwarp();                                           // every lane has read row pos0 + t for the last time
             if (lane == 0) mbar_arrive(empty0 + 8 * oslot);
             slot_l = slot_l + 1 == ring ? 0 : slot_l + 1;
@@ -490,7 +491,7 @@ int svm_tile_cost(int cols_left, int rows_left, int units)
     return busiest * 16 + total;
 }
 
-template <int C>
+template <int C, bool MULTI>
 static void launch_pass(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_items, int nitems, const float* d_hist,
                         const SvmParams& p, const SvmPass& S, int grid, cudaStream_t st)
 {
@@ -499,8 +500,8 @@ static void launch_pass(const FrameSet& fs, const LevelDesc* d_levels, const Svm
     int dev = 0;
     cudaGetDevice(&dev);
     if (!attr_set[dev & 63])
-        attr_set[dev & 63] = cudaFuncSetAttribute(svm_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) == cudaSuccess;
-    svm_kernel<C><<<grid, kSvmThreads, kSmemBytes, st>>>(fs, d_levels, d_items, nitems, d_hist, p, S);
+        attr_set[dev & 63] = cudaFuncSetAttribute(svm_kernel<C, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) == cudaSuccess;
+    svm_kernel<C, MULTI><<<grid, kSvmThreads, kSmemBytes, st>>>(fs, d_levels, d_items, nitems, d_hist, p, S);
 }
 
 // items1 / items2: the tile lists for one-detector passes (svm_tile_wx(.., 1) wide) and two-detector passes (16 wide)
@@ -518,16 +519,16 @@ void launch_svm(const FrameSet& fs, const LevelDesc* d_levels, const SvmItem* d_
         const int nitems = nd == 2 ? nitems2 : nitems1;
         if (nitems > 0) {
             const int grid = std::max(1, std::min(num_sms, nitems));
+            // windows up to 8 blocks wide are one chunk of C = win_bx columns; wider ones are 2 or 3 chunks of C = 5 .. 8
+#define HOGB200_SVM_CASE(c) case c: if (S.nchunks == 1) launch_pass<c, false>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); \
+                                    else launch_pass<(c < 5 ? 5 : c), true>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
             switch (C) {
-                case 1: launch_pass<1>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 2: launch_pass<2>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 3: launch_pass<3>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 4: launch_pass<4>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 5: launch_pass<5>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 6: launch_pass<6>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                case 7: launch_pass<7>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
-                default: launch_pass<8>(fs, d_levels, items, nitems, d_hist, p, S, grid, st); break;
+                HOGB200_SVM_CASE(1) HOGB200_SVM_CASE(2) HOGB200_SVM_CASE(3) HOGB200_SVM_CASE(4)
+                HOGB200_SVM_CASE(5) HOGB200_SVM_CASE(6) HOGB200_SVM_CASE(7)
+                default: if (S.nchunks == 1) launch_pass<8, false>(fs, d_levels, items, nitems, d_hist, p, S, grid, st);
+                         else launch_pass<8, true>(fs, d_levels, items, nitems, d_hist, p, S, grid, st);
             }
+#undef HOGB200_SVM_CASE
         }
         d += nd;
     }

@@ -1,4 +1,5 @@
-baseline/_ref/ref_cuda_bench 2>&1 | tee gpurun_out/r02_ref_cuda_kernels.txt
-echo "--- ours, same GPU: one 1080p frame per launch (all 44 levels in 3 launches), then 4 frames per launch" | tee -a gpurun_out/r02_ref_cuda_kernels.txt
-python tools/prof_one.py 6 2>&1 | tee -a gpurun_out/r02_ref_cuda_kernels.txt
-python tools/prof_batch.py 6 2>&1 | tee -a gpurun_out/r02_ref_cuda_kernels.txt
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python tools/prof_batch.py 6
+python bench.py --workload vga --quick --no-cpu --steps 10 --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('vga', d['value'], d['roofline']['stage_ms_per_launch'])"
+HOGB200_LIB=build_variants/libhogb200_r1c2.so python bench.py --workload vga --quick --no-cpu --steps 10 --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('vga chunks=2', d['value'], d['roofline']['stage_ms_per_launch'])"
+python bench.py --workload kitti --quick --no-cpu --steps 10 --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('kitti', d['value'], d['roofline']['stage_ms_per_launch'])"
