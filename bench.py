@@ -318,8 +318,9 @@ def main():
             out = [np.concatenate(out[i * NSLOTS:(i + 1) * NSLOTS]) for i in range(len(out) // NSLOTS)]
         t = hog.lastTimings()
         if gather:                                 # boxes of all ranks -> rank 0, frame order, on the host (shard.py)
-            merged = gather_detections(dict(zip(my_ids, out)), n_global, rank, world, group=host_group)
-            assert merged is None or len(merged) == n_global
+            n_all = len(out) * world                # (a leg may run a prefix of the step's frames)
+            merged = gather_detections(dict(zip(my_ids[:len(out)], out)), n_all, rank, world, group=host_group)
+            assert merged is None or len(merged) == n_all
         return sum(len(o) for o in out), t["kernel_launches"], t["candidates"]
 
     def timed(frames, steps, gather=False, capacity=1 << 20, seconds=None, pipelined=True):
@@ -367,7 +368,15 @@ def main():
     ms_e2e, nrects_e2e, _, cands_e2e, _ = timed(pinned_np, args.steps, gather=True)
     fps_e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
     h2d = BATCH * W * H * CN
-    d2h = int(16 * ((BATCH + 63) // 64) + 16 * max(cands_e2e, 0) / max(args.steps, 1))
+    nchunks = (BATCH + 63) // 64
+
+    def d2h_bytes(cands_per_step, rects_per_step):
+        """device -> host bytes of a step: one 16-byte count per chunk, then either the candidates (16 B each, host tail)
+        or -- from 1 024 candidates per chunk, where the tail runs on the device -- the per-segment counts and the rects"""
+        if cands_per_step / nchunks >= 1024:
+            return int(16 * nchunks + 4 * (BATCH * NSLOTS + nchunks) + 16 * rects_per_step)
+        return int(16 * nchunks + 16 * cands_per_step)
+    d2h = d2h_bytes(cands_e2e / max(args.steps, 1), nrects_e2e / max(args.steps, 1))
     # the blocking entry point (one batch at a time, every call ends with a synchronisation), for comparison
     timed(dev, 3, pipelined=False)
     ms_b, _, _, _, _ = timed(dev, args.steps, pipelined=False)
@@ -403,7 +412,7 @@ def main():
                                  "candidates_per_step": cands_h / args.steps, "candidates_per_frame": cands_h / args.steps / BATCH,
                                  "detections_per_step": nrects_h / args.steps,
                                  "h2d_bytes_per_step": h2d,
-                                 "d2h_bytes_per_step": int(16 * ((BATCH + 63) // 64) + 16 * cands_h / args.steps),
+                                 "d2h_bytes_per_step": d2h_bytes(cands_h / args.steps, nrects_h / args.steps),
                                  "ms_per_step": ms_h / args.steps}
         hog.setHitThreshold(HIT); hog.setGroupThreshold(GROUP)
 

@@ -123,6 +123,30 @@ public:
         found.assign(frames.size() * nslots, std::vector<Rect>());
         for (size_t i = 0; i + 1 < offs.size(); i++) found[i].assign(rects_.begin() + offs[i], rects_.begin() + offs[i + 1]);
     }
+    // the same batch asynchronously (two may be in flight): submit batch k + 1, then collect batch k, so that the uploads
+    // and kernels of one batch overlap the tail of the other.  The frames' pixels must stay valid until collect.
+    int submitBatch(const std::vector<Image>& frames, int nslots = 1)
+    {
+        std::vector<hogb200_image> im;
+        for (const Image& f : frames) im.push_back(f.c());
+        int ticket = -1;
+        check(hogb200_submit_batch(h_, im.data(), (int)im.size(), nslots, &ticket));
+        inflight_[ticket] = frames.size() * nslots;
+        return ticket;
+    }
+    void collectBatch(int ticket, std::vector<std::vector<Rect> >& found)
+    {
+        const size_t nseg = ticket >= 0 && ticket < 2 ? inflight_[ticket] : 0;
+        std::vector<size_t> offs(nseg + 1);
+        for (;;) {
+            const int rc = hogb200_collect_batch(h_, ticket, rects_.data(), rects_.size(), offs.data());
+            if (rc == HOGB200_CAPACITY) { rects_.resize(rects_.size() * 8); continue; }     // the library keeps the results
+            check(rc);
+            break;
+        }
+        found.assign(nseg, std::vector<Rect>());
+        for (size_t i = 0; i + 1 < offs.size(); i++) found[i].assign(rects_.begin() + offs[i], rects_.begin() + offs[i + 1]);
+    }
     // compute (hog.cpp:490-534): descriptors of every window, getDescriptorSize() floats each
     void compute(const Image& img, std::vector<float>& descriptors)
     {
@@ -167,6 +191,7 @@ private:
     }
     hogb200_t* h_; Size win_;
     std::vector<Rect> rects_;
+    size_t inflight_[2] = {0, 0};        // output segments of the batches in flight, by ticket
 };
 
 // ---- cv::tbd (tbd.hpp:25-184)

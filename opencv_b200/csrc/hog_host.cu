@@ -153,6 +153,7 @@ struct hogb200 {
     DevBuf<uint8_t> d_roi_level, d_roi_pad;    // ROI path: the resized level and its reflect-101 padded copy
     Plan plan_roi;                             // single-level plan of the padded ROI level
     BatchJob jobs[2];                          // asynchronous batches in flight (ticket = index)
+    size_t job_cap = (size_t)1 << 18;          // candidates per chunk region of a job; grows when a chunk overflows
     cudaStream_t post_stream = nullptr;        // device tails of asynchronous batches (runs beside the next batch's kernels)
     cudaEvent_t post_done = nullptr;
     Plan plan, plan1, plan_grp;     // multi-scale plan, single-scale plan, multi-scale plan of the batch path (frame groups)
@@ -1346,7 +1347,7 @@ int hogb200_submit_batch(hogb200_t* h, const hogb200_image* frames, int nframes,
     }
     const size_t nchunks = J.chunks.size();
     // one candidate region per chunk (a chunk that overflows its region is re-run by collect)
-    const size_t cap = (size_t)1 << 18, region = align_up(16 + cap * sizeof(Candidate), 256);
+    const size_t cap = h->job_cap, region = align_up(16 + cap * sizeof(Candidate), 256);
     cudaStream_t st = h->stream;
     if (J.d_cand.cap < region * nchunks) { CK(cudaStreamSynchronize(st)); CK(cudaStreamSynchronize(h->post_stream)); }
     CK(J.d_cand.reserve(region * nchunks));
@@ -1405,7 +1406,12 @@ int hogb200_collect_batch(hogb200_t* h, int ticket, hogb200_rect* found, size_t 
         Plan P; P.lv = c.lv;                               // the level scales are all the tail needs of the plan
         if (n > c.cap) {
             // the chunk produced more candidates than its region holds: run it again through the blocking entry
-            // point, which sizes its list to the worst case
+            // point, which sizes its list to the worst case; later batches get regions twice the size of this demand
+            {
+                size_t want = h->job_cap;
+                while (want < 2 * n) want *= 2;
+                h->job_cap = std::min<size_t>(want, (size_t)std::max<long long>(c.nwindows, 1) * nslots * c.nf + 16);
+            }
             std::vector<hogb200_rect> part((size_t)std::max<long long>(c.nwindows, 1) * nslots * c.nf);
             std::vector<size_t> off((size_t)c.nf * nslots + 1);
             const double hit_now = h->hit_threshold; h->hit_threshold = J.hit_threshold;

@@ -35,7 +35,14 @@ KEYS = ["_total", "FFMA2", "FMUL2", "FADD2", "FFMA", "IDP", "UBLKCP", "SYNCS", "
 print("# %s  (cuobjdump -sass, static instruction counts per kernel; arch sm_100a)" % os.path.relpath(so))
 print("%-64s %s" % ("kernel", " ".join("%7s" % k.strip("_") for k in KEYS)))
 for k, c in kern.items():
-    name = re.sub(r"\((?!anonymous).*", "", demangle(k)).replace("hogk::(anonymous namespace)::", "").replace("hogk::<unnamed>::", "").replace("void ", "")
+    name = demangle(k)
+    if name.endswith(")"):                      # drop the parameter list: the '(' that matches the final ')'
+        depth = 0
+        for i in range(len(name) - 1, -1, -1):
+            depth += name[i] == ")"; depth -= name[i] == "("
+            if depth == 0:
+                name = name[:i]; break
+    name = name.replace("hogk::(anonymous namespace)::", "").replace("hogk::<unnamed>::", "").replace("void ", "").replace("(int)", "").replace("(bool)", "")
     print("%-64s %s" % (name[:64], " ".join("%7d" % c.get(x, 0) for x in KEYS)))
     if k in usage:
         print("    %s" % usage[k])
