@@ -339,7 +339,10 @@ def main():
                 while True:
                     done += 1
                     nxt = hog.submitBatch(frames, nslots=NSLOTS) if more() else None
+                    tw = time.perf_counter()
                     a, b, c = finish_step(hog.collectBatch(pending, capacity=capacity), gather)
+                    if os.environ.get("HOGB200_BENCH_VERBOSE"):
+                        print("  collect %.1f ms, %d candidates" % (1e3 * (time.perf_counter() - tw), c), file=sys.stderr)
                     nrects += a; launches += b; cands += c
                     if nxt is None:
                         break

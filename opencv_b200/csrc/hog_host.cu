@@ -1412,6 +1412,7 @@ int hogb200_collect_batch(hogb200_t* h, int ticket, hogb200_rect* found, size_t 
                 while (want < 2 * n) want *= 2;
                 h->job_cap = std::min<size_t>(want, (size_t)std::max<long long>(c.nwindows, 1) * nslots * c.nf + 16);
             }
+            if ((rc = ensure_cand(h, 2 * n))) return restore(rc);     // its first attempt then holds the list
             std::vector<hogb200_rect> part((size_t)std::max<long long>(c.nwindows, 1) * nslots * c.nf);
             std::vector<size_t> off((size_t)c.nf * nslots + 1);
             const double hit_now = h->hit_threshold; h->hit_threshold = J.hit_threshold;
