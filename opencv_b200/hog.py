@@ -359,6 +359,8 @@ class HOG:
 
     def collectBatch(self, ticket, capacity=1 << 16):
         """hogb200_collect_batch -> list (frame-major, slot-minor) of (N,4) int32 rect arrays."""
+        if ticket not in getattr(self, "_inflight", {}):
+            raise HogError(1, "no batch in flight under this ticket")
         keep, arr, nseg = self._inflight[ticket]
         while True:
             r = getattr(self, "_rect_buf", None)

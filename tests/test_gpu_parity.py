@@ -593,6 +593,40 @@ def test_submit_collect_equals_blocking_batch(hog, monkeypatch):
         hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
 
 
+def test_async_and_roi_edge_cases(hog, port):
+    """Edge cases of the entry points added in round 2: empty batches, bad tickets, 8UC3 frames through the ROI path,
+    a handle without detector, parameters captured at submit time."""
+    from opencv_b200 import HOG, HogError
+    t = hog.submitBatch([])
+    assert hog.collectBatch(t) == []
+    with pytest.raises(HogError):
+        hog.collectBatch(t)                                          # already collected
+    with pytest.raises(HogError):
+        hog._ck(hog._L.hogb200_collect_batch(hog._h, 7, None, 0, None))
+    bgra = synthetic_frame(77, 320, 256, 4, silhouettes=2)
+    bgr = np.ascontiguousarray(bgra[:, :, :3])
+    loc = np.stack([np.arange(-1, 31) * 8, (np.arange(-1, 31) * 5 % 17) * 8], 1).astype(np.int32)
+    loc = np.concatenate([loc, np.array([[400, 0], [0, 144], [-16, 8]], np.int32)])       # three outside the padded image
+    hog.setHitThreshold(-3.0)
+    f4, c4 = hog.detectROI(bgra, loc)
+    f3, c3 = hog.detectROI(bgr, loc)
+    assert np.array_equal(f3, f4) and np.array_equal(c3, c4) and (c4 == -10.0).any() and (c4 != -10.0).any()
+    r4, _ = hog.detectMultiScaleROI(bgra, [(1.0, loc), (1.21, loc), (3.0, loc)])   # the last level is smaller than the window
+    r3, cc = hog.detectMultiScaleROI(bgr, [(1.0, loc), (1.21, loc), (3.0, loc)])
+    assert np.array_equal(r3, r4) and (cc[2] == -10.0).all()
+    empty = HOG.create()
+    assert len(empty.detectROI(bgra, loc)[0]) == 0 and len(empty.detectMultiScaleROI(bgra, [(1.0, loc)])[0]) == 0
+    # the tail of an asynchronous batch uses the group threshold it was submitted with
+    frames = [synthetic_frame(9500 + i, 640, 480, 4, silhouettes=4) for i in range(3)]
+    hog.setHitThreshold(-1.5); hog.setGroupThreshold(2)
+    want = hog.detectMultiScaleBatch(frames)
+    t = hog.submitBatch(frames)
+    hog.setGroupThreshold(0)
+    got = hog.collectBatch(t)
+    assert all(np.array_equal(a, b) for a, b in zip(got, want)) and hog.getGroupThreshold() == 0
+    hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
 # ------------------------------------------------------------------ ROI variants (row f4)
 def _roi_locations(rng, w, h, n, pad=8, win=(64, 128)):
     """window origins on the 8-pixel lattice: inside the image, reaching into the padding, and a few outside it"""
