@@ -1153,7 +1153,7 @@ namespace {
 // Queue every frame group of a chunk (consecutive frames of one shape, plan P built for groups of `grp` frames) on the
 // handle's streams: uploads on the copy stream, double-buffered per group, kernels on the compute stream.
 int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, int nslots, const int* slots, const CandTarget* target,
-                int* launches)
+                int* launches, bool allow_lead_in = true)
 {
     int rc;
     cudaStream_t st = h->stream, cs = h->copy_stream;
@@ -1165,7 +1165,7 @@ int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, i
     bool lead_in = false;
     for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
     // (not when a batch is already in flight: its kernels hide this batch's first uploads)
-    lead_in = lead_in && nf > grp && batch_lead_in() && !h->jobs[0].active && !h->jobs[1].active;
+    lead_in = lead_in && allow_lead_in && nf > grp && batch_lead_in() && !h->jobs[0].active && !h->jobs[1].active;
     for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
         ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
         const int b = (int)(h->stage_seq++ % hogb200::kStage);     // staging slots: uploads run up to two groups ahead of the kernels
@@ -1269,8 +1269,8 @@ int hogb200_detect_multiscale_batch(hogb200_t* h, const hogb200_image* frames, i
     int total_launches = 0;
     size_t total_cands = 0;
     const int kChunk = 64;
-    std::vector<Candidate> c; std::vector<hogb200_rect> rects;
-    cudaStream_t st = h->stream, cs = h->copy_stream;
+    std::vector<Candidate> c;
+    cudaStream_t st = h->stream;
     if (h->timing) cudaEventRecord(h->ev[0], st);
     for (int i = 0; i < nframes; i++) if ((rc = check_image(&frames[i]))) return rc;
     int f0 = 0;
@@ -1363,7 +1363,8 @@ int hogb200_submit_batch(hogb200_t* h, const hogb200_image* frames, int nframes,
         c.cand_off = k * region; c.cap = cap; c.lv = h->plan_grp.lv; c.nwindows = h->plan_grp.nwindows; c.done = J.events[k];
         const CandTarget target{J.d_cand.p + c.cand_off, cap};
         CK(cudaMemsetAsync(target.p, 0, 16, st));
-        if ((rc = queue_chunk(h, h->plan_grp, fr, c.nf, grp, nslots, slots, &target, &J.launches))) return rc;
+        // (only the first chunk of a batch can find the stream idle)
+        if ((rc = queue_chunk(h, h->plan_grp, fr, c.nf, grp, nslots, slots, &target, &J.launches, k == 0))) return rc;
         CK(cudaMemcpyAsync(J.h_counts.p + 4 * k, target.p, 16, cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(c.done, st));
     }

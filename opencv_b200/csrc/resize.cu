@@ -66,10 +66,6 @@ __device__ __forceinline__ HRow hrow_px(unsigned p0, unsigned p1, unsigned a01)
     h.t[3] = (int)(__dp2a_hi(a01, hi, 0u) >> 4);
     return h;
 }
-__device__ __forceinline__ HRow hrow_gmem(const uint8_t* __restrict__ row, int sx0, int sx1, unsigned a01)
-{
-    return hrow_px(__ldg(reinterpret_cast<const unsigned*>(row) + sx0), __ldg(reinterpret_cast<const unsigned*>(row) + sx1), a01);
-}
 __device__ __forceinline__ HRow hrow_smem(unsigned addr, unsigned a01)
 {
     unsigned p0, p1;
