@@ -36,3 +36,7 @@ def test_cpp_example_tracks_the_walkers():
     tracks = [l for l in lines if l.startswith("track")]
     ages = [int(l.split("age ")[1].split(",")[0]) for l in tracks]
     assert len(tracks) >= 1 and max(ages) >= 6, p.stdout            # a walker is followed through most of the 12 frames
+    # the same loop on the asynchronous batch API (two batches in flight): identical detections and tracks
+    q = subprocess.run([EXE, "--pipelined"], capture_output=True, text=True, timeout=120)
+    assert q.returncode == 0, q.stderr
+    assert q.stdout == p.stdout
