@@ -83,13 +83,15 @@ struct Plan {
     int nlevels_param = 0; double scale0 = 0; int win_w = 0, win_h = 0, sx = 0, sy = 0;
     bool single_level = false;
     int group = 1;                       // frames per launch the work lists were built for
+    int lane_group = 1;                  // frames between the two workspace lanes (the chunk's full group size, >= group)
     long long pyr_stride = 0, hist_stride = 0;   // per-frame strides inside d_pyr (bytes) / d_hist (floats)
     int strip = 0;                       // block rows per histogram work item (chosen by balance_strip)
     std::vector<LevelHost> lv;
     long long hist_floats = 0, score_floats = 0, pyr_pixels = 0, nblocks = 0, nwindows = 0;
     size_t pyr_bytes = 0;
     int n_resize = 0, n_hist = 0, n_svm = 0, n_svm2 = 0;
-    DevBuf<LevelDesc> d_levels; DevBuf<ResizeCoef> d_xtab, d_ytab;
+    DevBuf<LevelDesc> d_levels, d_levels_b;      // level tables of workspace lane 0 / lane 1 (same levels, pyramid one group further)
+    DevBuf<ResizeCoef> d_xtab, d_ytab;
     DevBuf<ResizeItem> d_ritems; DevBuf<HistItem> d_hitems; DevBuf<SvmItem> d_sitems, d_sitems2;   // tiles of one-detector / two-detector scoring passes
     const uint8_t* pyr_base = nullptr;   // pyramid buffer the level pointers were built for
     bool valid = false;
@@ -136,6 +138,11 @@ struct hogb200 {
     std::vector<float> det_host[kMaxDet];           // as given (column-major blocks + optional bias), for hogb200_save
     // streams
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+    // The batch path alternates its frame groups between two LANES: lane 0 = `stream`, lane 1 = `lane_stream`, each with its
+    // own pyramid / histogram workspace, level table and histogram work queue, so that the ragged end of one group's
+    // persistent kernels is filled by the next group's kernels (HOGB200_LANES=1 switches it off).
+    cudaStream_t lane_stream = nullptr;
+    cudaEvent_t lane_fork = nullptr, lane_join = nullptr;
     // staging slots of the batch path rotate ACROSS calls (a batch never starts on the slot the previous one ended on)
     static constexpr int kStage = 3;
     cudaEvent_t up_done[kStage] = {nullptr, nullptr, nullptr}, fr_done[kStage] = {nullptr, nullptr, nullptr};
@@ -283,14 +290,15 @@ int balance_strip(const std::vector<LevelHost>& lv, int group, int workers)
     return best;
 }
 
-int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group = 1)
+int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group = 1, int lane_group = 0)
 {
-    if (P.valid && P.W == W && P.H == H && P.cn == cn && P.single_level == single && P.group == group &&
+    if (lane_group < group) lane_group = group;
+    if (P.valid && P.W == W && P.H == H && P.cn == cn && P.single_level == single && P.group == group && P.lane_group == lane_group &&
         P.nlevels_param == h->nlevels && P.scale0 == h->scale0 && P.win_w == h->g.win_w && P.win_h == h->g.win_h &&
         P.sx == h->win_stride_x && P.sy == h->win_stride_y && P.pyr_base == h->d_pyr.p)
         return HOGB200_OK;
     P.valid = false;
-    P.W = W; P.H = H; P.cn = cn; P.single_level = single; P.group = group;
+    P.W = W; P.H = H; P.cn = cn; P.single_level = single; P.group = group; P.lane_group = lane_group;
     P.nlevels_param = h->nlevels; P.scale0 = h->scale0; P.win_w = h->g.win_w; P.win_h = h->g.win_h;
     P.sx = h->win_stride_x; P.sy = h->win_stride_y;
 
@@ -393,20 +401,25 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     P.pyr_stride = (long long)align_up(pyr, 256);
     P.hist_stride = P.hist_floats;
     P.pyr_bytes = pyr;
-    CK(h->d_pyr.reserve((size_t)P.pyr_stride * group + 256));
+    CK(h->d_pyr.reserve((size_t)P.pyr_stride * lane_group * 2 + 256));   // two lanes (see hogb200::lane_stream)
+    std::vector<LevelDesc> descs_b = descs;
     for (size_t i = 0; i < descs.size(); i++)
-        if (P.lv[i].mode != 0) descs[i].img = h->d_pyr.p + P.lv[i].img_off;
+        if (P.lv[i].mode != 0) {
+            descs[i].img = h->d_pyr.p + P.lv[i].img_off;
+            descs_b[i].img = descs[i].img + (size_t)P.pyr_stride * lane_group;
+        }
     P.pyr_base = h->d_pyr.p;
-    CK(h->d_hist.reserve((size_t)P.hist_stride * group + 64));
+    CK(h->d_hist.reserve((size_t)P.hist_stride * lane_group * 2 + 64));
     P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size(); P.n_svm2 = (int)sitems2.size();
     cudaStream_t st = h->stream;
-    CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use
+    CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use,
+    CK(cudaStreamSynchronize(h->lane_stream));      // on either lane
     auto up = [&](auto& buf, const auto& v) -> cudaError_t {
         cudaError_t e = buf.reserve(v.size() + 1);
         if (e != cudaSuccess || v.empty()) return e;
         return cudaMemcpy(buf.p, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
     };
-    CK(up(P.d_levels, descs)); CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
+    CK(up(P.d_levels, descs)); CK(up(P.d_levels_b, descs_b)); CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
     CK(up(P.d_ritems, ritems)); CK(up(P.d_hitems, hitems)); CK(up(P.d_sitems, sitems)); CK(up(P.d_sitems2, sitems2));
     P.valid = true;
     return HOGB200_OK;
@@ -550,24 +563,27 @@ GroupTrace g_trace;
 struct CandTarget { unsigned char* p; size_t cap; };
 
 int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, const int* slots, float thresh,
-                float* d_scores, int tag, int* launches, const CandTarget* target = nullptr)
+                float* d_scores, int tag, int* launches, const CandTarget* target = nullptr, int lane = 0)
 {
     const CandTarget own{h->d_cand.p, h->cand_cap};
     const CandTarget& ct = target ? *target : own;
-    cudaStream_t st = h->stream;
+    cudaStream_t st = lane ? h->lane_stream : h->stream;
+    const LevelDesc* d_levels = lane ? P.d_levels_b.p : P.d_levels.p;
+    float* d_hist = h->d_hist.p + (lane ? (size_t)P.hist_stride * P.lane_group : 0);
+    unsigned int* d_queue = h->d_queue.p + 2 * lane;
     FrameSet fs; memset(&fs, 0, sizeof fs);
     for (int i = 0; i < nframes; i++) { fs.base[i] = f[i].dev; fs.pitch[i] = f[i].pitch; }
     fs.nframes = nframes; fs.pyr_stride = P.pyr_stride; fs.hist_stride = P.hist_stride;
     if (h->timing) cudaEventRecord(h->ev[1], st);
     if (P.n_resize) {
-        launch_resize(fs, P.W, P.H, P.cn, P.d_levels.p, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
+        launch_resize(fs, P.W, P.H, P.cn, d_levels, P.d_xtab.p, P.d_ytab.p, P.d_ritems.p, P.n_resize, st);
         (*launches)++;
         g_watchdog.mark(st, "resize", nframes);
     }
     if (h->timing) cudaEventRecord(h->ev[2], st);
     if (P.n_hist) {
-        launch_hist(fs, P.d_levels.p, P.d_hitems.p, P.n_hist, h->d_queue.p, h->num_sms, P.cn, h->gamma,
-                    h->weights, (float)h->l2hys, h->d_hist.p, st);
+        launch_hist(fs, d_levels, P.d_hitems.p, P.n_hist, d_queue, h->num_sms, P.cn, h->gamma,
+                    h->weights, (float)h->l2hys, d_hist, st);
         (*launches)++;
         g_watchdog.mark(st, "hist", nframes);
     }
@@ -582,7 +598,7 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
         sp.cand = reinterpret_cast<Candidate*>(ct.p + 16);
         sp.cand_count = reinterpret_cast<unsigned int*>(ct.p);
         sp.cand_cap = (unsigned int)ct.cap; sp.tag = tag;
-        launch_svm(fs, P.d_levels.p, P.d_sitems.p, P.n_svm, P.d_sitems2.p, P.n_svm2, h->d_hist.p, sp, h->num_sms, st);
+        launch_svm(fs, d_levels, P.d_sitems.p, P.n_svm, P.d_sitems2.p, P.n_svm2, d_hist, sp, h->num_sms, st);
         (*launches) += ndet >= 2 && P.n_svm2 ? (ndet + 1) / 2 : ndet;
         g_watchdog.mark(st, "svm", nframes);
     }
@@ -807,6 +823,9 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->lane_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->lane_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->lane_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->post_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->post_done, cudaEventDisableTiming);
     for (int i = 0; i < hogb200::kStage && e == cudaSuccess; i++) {
@@ -816,7 +835,7 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&h->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
     if (e == cudaSuccess) e = h->d_queue.reserve(4);
-    if (e == cudaSuccess) e = cudaMemset(h->d_queue.p, 0, 4 * sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemset(h->d_queue.p, 0, 4 * sizeof(unsigned int));     // two queues: [head, finished] per lane
     if (e != cudaSuccess) {
         cudaGetLastError();
         hogb200_destroy(h);
@@ -841,7 +860,7 @@ void hogb200_destroy(hogb200_t* h)
     h->d_roi_level.release(); h->d_roi_pad.release();
     for (Plan& P : h->plan_part) plans.push_back(&P);
     for (Plan* P : plans) {
-        P->d_levels.release(); P->d_xtab.release(); P->d_ytab.release();
+        P->d_levels.release(); P->d_levels_b.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release(); P->d_sitems2.release();
     }
     for (int i = 0; i < hogb200::kStage; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
@@ -849,6 +868,9 @@ void hogb200_destroy(hogb200_t* h)
     for (BatchJob& J : h->jobs) { J.d_cand.release(); J.h_counts.release(); for (cudaEvent_t e : J.events) cudaEventDestroy(e); }
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
     if (h->post_done) cudaEventDestroy(h->post_done);
+    if (h->lane_stream) { cudaStreamSynchronize(h->lane_stream); cudaStreamDestroy(h->lane_stream); }
+    if (h->lane_fork) cudaEventDestroy(h->lane_fork);
+    if (h->lane_join) cudaEventDestroy(h->lane_join);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     delete h;
@@ -1083,6 +1105,13 @@ bool batch_lead_in()
     return v;
 }
 
+// two workspace lanes in the batch path (HOGB200_LANES=1 keeps everything on one stream)
+bool batch_lanes()
+{
+    static const bool v = [] { const char* e = getenv("HOGB200_LANES"); return !e || atoi(e) != 1; }();
+    return v;
+}
+
 // Frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup).  Measured on B200 (bench.py
 // --workload ..., profiles/): 4 suits 1080p and KITTI-sized frames; frames whose whole pyramid is a few megapixels
 // (VGA) need more per launch to fill the persistent kernels' queues; at 4K two base frames (66 MB) still sit in L2
@@ -1166,37 +1195,44 @@ int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, i
     for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
     // (not when a batch is already in flight: its kernels hide this batch's first uploads)
     lead_in = lead_in && allow_lead_in && nf > grp && batch_lead_in() && !h->jobs[0].active && !h->jobs[1].active;
+    // two lanes: even groups on the handle's stream, odd ones on lane_stream with the second workspace; lane 1 starts
+    // behind everything queued on the handle's stream so far and is joined back before the chunk's count is read
+    const bool lanes = batch_lanes() && !h->timing && nf > grp;
+    if (lanes) { CK(cudaEventRecord(h->lane_fork, st)); CK(cudaStreamWaitEvent(h->lane_stream, h->lane_fork, 0)); }
     for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
         ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
         const int b = (int)(h->stage_seq++ % hogb200::kStage);     // staging slots: uploads run up to two groups ahead of the kernels
+        const int lane = lanes ? (gi & 1) : 0;
+        cudaStream_t ks = lane ? h->lane_stream : st;              // the stream of this group's kernels
         FrameRef f[kMaxGroup];
         bool any_host = false;
         for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
         if (any_host) CK(cudaStreamWaitEvent(cs, h->fr_done[b], 0));
-        else CK(cudaStreamWaitEvent(st, h->fr_done[b], 0));
-        g_trace.mark(0, any_host ? cs : st);
+        else CK(cudaStreamWaitEvent(ks, h->fr_done[b], 0));
+        g_trace.mark(0, any_host ? cs : ks);
         for (int j = 0; j < ng; j++) {
             const hogb200_image* im = fr + g0 + j;
             // host frames: upload on the copy stream, overlapping the previous group's kernels
-            if ((rc = stage_frame(h, im, b * kMaxGroup + j, im->on_device ? st : cs, f[j]))) return rc;
+            if ((rc = stage_frame(h, im, b * kMaxGroup + j, im->on_device ? ks : cs, f[j]))) return rc;
         }
         if (any_host) {
             CK(cudaEventRecord(h->up_done[b], cs));
-            CK(cudaStreamWaitEvent(st, h->up_done[b], 0));
+            CK(cudaStreamWaitEvent(ks, h->up_done[b], 0));
         }
-        g_trace.mark(1, any_host ? cs : st);
-        g_trace.mark(2, st);
+        g_trace.mark(1, any_host ? cs : ks);
+        g_trace.mark(2, ks);
         // a group smaller than grp runs on a plan of its own size: work lists dealt for grp frames leave the
         // persistent kernels unbalanced when most of their items belong to absent frames
         Plan* Pg = &P;
         if (ng != grp) {
             Pg = &h->plan_part[ng];
-            if ((rc = build_plan(h, *Pg, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, ng))) return rc;
+            if ((rc = build_plan(h, *Pg, fr->width, fr->height, fr->channels == 3 ? 4 : fr->channels, false, ng, grp))) return rc;
         }
-        if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches, target))) return rc;
-        CK(cudaEventRecord(h->fr_done[b], st));
-        g_trace.mark(3, st);
+        if ((rc = queue_group(h, *Pg, f, ng, nslots, slots, (float)h->hit_threshold, nullptr, g0 << 20, &total_launches, target, lane))) return rc;
+        CK(cudaEventRecord(h->fr_done[b], ks));
+        g_trace.mark(3, ks);
     }
+    if (lanes) { CK(cudaEventRecord(h->lane_join, h->lane_stream)); CK(cudaStreamWaitEvent(st, h->lane_join, 0)); }
     return HOGB200_OK;
 }
 
