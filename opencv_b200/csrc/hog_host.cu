@@ -90,7 +90,7 @@ struct Plan {
     long long hist_floats = 0, score_floats = 0, pyr_pixels = 0, nblocks = 0, nwindows = 0;
     size_t pyr_bytes = 0;
     int n_resize = 0, n_hist = 0, n_svm = 0, n_svm2 = 0;
-    DevBuf<LevelDesc> d_levels, d_levels_b;      // level tables of workspace lane 0 / lane 1 (same levels, pyramid one group further)
+    DevBuf<LevelDesc> d_levels, d_levels_l[3];   // level tables of workspace lane 0 / lanes 1..3 (same levels, pyramids lane_group frames apart)
     DevBuf<ResizeCoef> d_xtab, d_ytab;
     DevBuf<ResizeItem> d_ritems; DevBuf<HistItem> d_hitems; DevBuf<SvmItem> d_sitems, d_sitems2;   // tiles of one-detector / two-detector scoring passes
     const uint8_t* pyr_base = nullptr;   // pyramid buffer the level pointers were built for
@@ -138,14 +138,16 @@ struct hogb200 {
     std::vector<float> det_host[kMaxDet];           // as given (column-major blocks + optional bias), for hogb200_save
     // streams
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
-    // The batch path alternates its frame groups between two LANES: lane 0 = `stream`, lane 1 = `lane_stream`, each with its
-    // own pyramid / histogram workspace, level table and histogram work queue, so that the ragged end of one group's
-    // persistent kernels is filled by the next group's kernels (HOGB200_LANES=1 switches it off).
-    cudaStream_t lane_stream = nullptr;
-    cudaEvent_t lane_fork = nullptr, lane_join = nullptr;
+    // The batch path deals its frame groups round-robin to LANES: lane 0 = `stream`, lanes 1.. = `lane_stream[]`, each with
+    // its own pyramid / histogram workspace, level table and histogram work queue, so that the ragged end of one group's
+    // persistent kernels (and the launch gaps between its three kernels) are filled by the next group's kernels
+    // (HOGB200_LANES=n, 1 .. kMaxLanes; 1 switches it off).
+    static constexpr int kMaxLanes = 4;
+    cudaStream_t lane_stream[kMaxLanes - 1] = {nullptr, nullptr, nullptr};
+    cudaEvent_t lane_fork = nullptr, lane_join[kMaxLanes - 1] = {nullptr, nullptr, nullptr};
     // staging slots of the batch path rotate ACROSS calls (a batch never starts on the slot the previous one ended on)
-    static constexpr int kStage = 3;
-    cudaEvent_t up_done[kStage] = {nullptr, nullptr, nullptr}, fr_done[kStage] = {nullptr, nullptr, nullptr};
+    static constexpr int kStage = 4;
+    cudaEvent_t up_done[kStage] = {nullptr, nullptr, nullptr, nullptr}, fr_done[kStage] = {nullptr, nullptr, nullptr, nullptr};
     unsigned stage_seq = 0;
     // workspace
     DevBuf<uint8_t> d_frame[kStage * kMaxGroup]; DevBuf<uint8_t> d_raw[kStage * kMaxGroup]; DevBuf<uint8_t> d_pyr; DevBuf<float> d_hist; DevBuf<float> d_scores;
@@ -258,6 +260,17 @@ bool is_exact_half(int src_w, int src_h, int dst_w, int dst_h)
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// workspace lanes of the batch path (HOGB200_LANES=n overrides, 1 = everything on one stream)
+int batch_lanes()
+{
+    static const int v = [] {
+        const char* e = getenv("HOGB200_LANES");
+        const int n = e ? atoi(e) : 2;
+        return n >= 1 && n <= hogb200::kMaxLanes ? n : 2;
+    }();
+    return v;
+}
 
 // Block rows per histogram work item.  The kernel's workers (warps) pull items longest-first from a queue, so the
 // finishing time is that of greedy list scheduling: simulate it for every candidate height and keep the best
@@ -401,25 +414,29 @@ int build_plan(hogb200* h, Plan& P, int W, int H, int cn, bool single, int group
     P.pyr_stride = (long long)align_up(pyr, 256);
     P.hist_stride = P.hist_floats;
     P.pyr_bytes = pyr;
-    CK(h->d_pyr.reserve((size_t)P.pyr_stride * lane_group * 2 + 256));   // two lanes (see hogb200::lane_stream)
-    std::vector<LevelDesc> descs_b = descs;
+    const int nlanes = single ? 1 : batch_lanes();
+    CK(h->d_pyr.reserve((size_t)P.pyr_stride * lane_group * nlanes + 256));   // one workspace per lane (see hogb200::lane_stream)
     for (size_t i = 0; i < descs.size(); i++)
-        if (P.lv[i].mode != 0) {
-            descs[i].img = h->d_pyr.p + P.lv[i].img_off;
-            descs_b[i].img = descs[i].img + (size_t)P.pyr_stride * lane_group;
-        }
+        if (P.lv[i].mode != 0) descs[i].img = h->d_pyr.p + P.lv[i].img_off;
     P.pyr_base = h->d_pyr.p;
-    CK(h->d_hist.reserve((size_t)P.hist_stride * lane_group * 2 + 64));
+    CK(h->d_hist.reserve((size_t)P.hist_stride * lane_group * nlanes + 64));
     P.n_resize = (int)ritems.size(); P.n_hist = (int)hitems.size(); P.n_svm = (int)sitems.size(); P.n_svm2 = (int)sitems2.size();
     cudaStream_t st = h->stream;
     CK(cudaStreamSynchronize(st));      // the previous plan's tables may still be in use,
-    CK(cudaStreamSynchronize(h->lane_stream));      // on either lane
+    for (cudaStream_t ls : h->lane_stream) CK(cudaStreamSynchronize(ls));      // on any lane
     auto up = [&](auto& buf, const auto& v) -> cudaError_t {
         cudaError_t e = buf.reserve(v.size() + 1);
         if (e != cudaSuccess || v.empty()) return e;
         return cudaMemcpy(buf.p, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
     };
-    CK(up(P.d_levels, descs)); CK(up(P.d_levels_b, descs_b)); CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
+    CK(up(P.d_levels, descs));
+    for (int l = 1; l < nlanes; l++) {
+        std::vector<LevelDesc> dl = descs;
+        for (size_t i = 0; i < dl.size(); i++)
+            if (P.lv[i].mode != 0) dl[i].img = descs[i].img + (size_t)P.pyr_stride * lane_group * l;
+        CK(up(P.d_levels_l[l - 1], dl));
+    }
+    CK(up(P.d_xtab, xtab)); CK(up(P.d_ytab, ytab));
     CK(up(P.d_ritems, ritems)); CK(up(P.d_hitems, hitems)); CK(up(P.d_sitems, sitems)); CK(up(P.d_sitems2, sitems2));
     P.valid = true;
     return HOGB200_OK;
@@ -567,9 +584,9 @@ int queue_group(hogb200* h, Plan& P, const FrameRef* f, int nframes, int ndet, c
 {
     const CandTarget own{h->d_cand.p, h->cand_cap};
     const CandTarget& ct = target ? *target : own;
-    cudaStream_t st = lane ? h->lane_stream : h->stream;
-    const LevelDesc* d_levels = lane ? P.d_levels_b.p : P.d_levels.p;
-    float* d_hist = h->d_hist.p + (lane ? (size_t)P.hist_stride * P.lane_group : 0);
+    cudaStream_t st = lane ? h->lane_stream[lane - 1] : h->stream;
+    const LevelDesc* d_levels = lane ? P.d_levels_l[lane - 1].p : P.d_levels.p;
+    float* d_hist = h->d_hist.p + (size_t)P.hist_stride * P.lane_group * lane;
     unsigned int* d_queue = h->d_queue.p + 2 * lane;
     FrameSet fs; memset(&fs, 0, sizeof fs);
     for (int i = 0; i < nframes; i++) { fs.base[i] = f[i].dev; fs.pitch[i] = f[i].pitch; }
@@ -823,9 +840,11 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->lane_stream, cudaStreamNonBlocking);
+    for (int l = 0; l < hogb200::kMaxLanes - 1 && e == cudaSuccess; l++) {
+        e = cudaStreamCreateWithFlags(&h->lane_stream[l], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->lane_join[l], cudaEventDisableTiming);
+    }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->lane_fork, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->lane_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->post_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->post_done, cudaEventDisableTiming);
     for (int i = 0; i < hogb200::kStage && e == cudaSuccess; i++) {
@@ -834,8 +853,8 @@ int hogb200_create(const hogb200_geom* geom, int device, hogb200_t** out)
     }
     for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&h->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
-    if (e == cudaSuccess) e = h->d_queue.reserve(4);
-    if (e == cudaSuccess) e = cudaMemset(h->d_queue.p, 0, 4 * sizeof(unsigned int));     // two queues: [head, finished] per lane
+    if (e == cudaSuccess) e = h->d_queue.reserve(2 * hogb200::kMaxLanes);
+    if (e == cudaSuccess) e = cudaMemset(h->d_queue.p, 0, 2 * hogb200::kMaxLanes * sizeof(unsigned int));     // [head, finished] per lane
     if (e != cudaSuccess) {
         cudaGetLastError();
         hogb200_destroy(h);
@@ -860,7 +879,7 @@ void hogb200_destroy(hogb200_t* h)
     h->d_roi_level.release(); h->d_roi_pad.release();
     for (Plan& P : h->plan_part) plans.push_back(&P);
     for (Plan* P : plans) {
-        P->d_levels.release(); P->d_levels_b.release(); P->d_xtab.release(); P->d_ytab.release();
+        P->d_levels.release(); for (auto& b : P->d_levels_l) b.release(); P->d_xtab.release(); P->d_ytab.release();
         P->d_ritems.release(); P->d_hitems.release(); P->d_sitems.release(); P->d_sitems2.release();
     }
     for (int i = 0; i < hogb200::kStage; i++) { if (h->up_done[i]) cudaEventDestroy(h->up_done[i]); if (h->fr_done[i]) cudaEventDestroy(h->fr_done[i]); }
@@ -868,9 +887,9 @@ void hogb200_destroy(hogb200_t* h)
     for (BatchJob& J : h->jobs) { J.d_cand.release(); J.h_counts.release(); for (cudaEvent_t e : J.events) cudaEventDestroy(e); }
     if (h->post_stream) cudaStreamDestroy(h->post_stream);
     if (h->post_done) cudaEventDestroy(h->post_done);
-    if (h->lane_stream) { cudaStreamSynchronize(h->lane_stream); cudaStreamDestroy(h->lane_stream); }
+    for (cudaStream_t ls : h->lane_stream) if (ls) { cudaStreamSynchronize(ls); cudaStreamDestroy(ls); }
     if (h->lane_fork) cudaEventDestroy(h->lane_fork);
-    if (h->lane_join) cudaEventDestroy(h->lane_join);
+    for (cudaEvent_t ev : h->lane_join) if (ev) cudaEventDestroy(ev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     delete h;
@@ -1105,12 +1124,6 @@ bool batch_lead_in()
     return v;
 }
 
-// two workspace lanes in the batch path (HOGB200_LANES=1 keeps everything on one stream)
-bool batch_lanes()
-{
-    static const bool v = [] { const char* e = getenv("HOGB200_LANES"); return !e || atoi(e) != 1; }();
-    return v;
-}
 
 // Frames per launch in the batch path (HOGB200_GROUP overrides, 1 .. kMaxGroup).  Measured on B200 (bench.py
 // --workload ..., profiles/): 4 suits 1080p and KITTI-sized frames; frames whose whole pyramid is a few megapixels
@@ -1195,15 +1208,18 @@ int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, i
     for (int j = 0; j < nf; j++) lead_in |= !fr[j].on_device;
     // (not when a batch is already in flight: its kernels hide this batch's first uploads)
     lead_in = lead_in && allow_lead_in && nf > grp && batch_lead_in() && !h->jobs[0].active && !h->jobs[1].active;
-    // two lanes: even groups on the handle's stream, odd ones on lane_stream with the second workspace; lane 1 starts
-    // behind everything queued on the handle's stream so far and is joined back before the chunk's count is read
-    const bool lanes = batch_lanes() && !h->timing && nf > grp;
-    if (lanes) { CK(cudaEventRecord(h->lane_fork, st)); CK(cudaStreamWaitEvent(h->lane_stream, h->lane_fork, 0)); }
+    // groups are dealt round-robin to the lanes (lane 0 = the handle's stream); the other lanes start behind everything
+    // queued on the handle's stream so far and are joined back before the chunk's count is read
+    const int nlanes = (h->timing || nf <= grp) ? 1 : batch_lanes();
+    if (nlanes > 1) {
+        CK(cudaEventRecord(h->lane_fork, st));
+        for (int l = 1; l < nlanes; l++) CK(cudaStreamWaitEvent(h->lane_stream[l - 1], h->lane_fork, 0));
+    }
     for (int g0 = 0, gi = 0, ng = 0; g0 < nf; g0 += ng, gi++) {
         ng = (lead_in && gi == 0) ? 1 : (lead_in && gi == 1 && grp > 2) ? grp - 1 : std::min(grp, nf - g0);
         const int b = (int)(h->stage_seq++ % hogb200::kStage);     // staging slots: uploads run up to two groups ahead of the kernels
-        const int lane = lanes ? (gi & 1) : 0;
-        cudaStream_t ks = lane ? h->lane_stream : st;              // the stream of this group's kernels
+        const int lane = gi % nlanes;
+        cudaStream_t ks = lane ? h->lane_stream[lane - 1] : st;    // the stream of this group's kernels
         FrameRef f[kMaxGroup];
         bool any_host = false;
         for (int j = 0; j < ng; j++) any_host |= !fr[g0 + j].on_device;
@@ -1232,7 +1248,7 @@ int queue_chunk(hogb200* h, Plan& P, const hogb200_image* fr, int nf, int grp, i
         CK(cudaEventRecord(h->fr_done[b], ks));
         g_trace.mark(3, ks);
     }
-    if (lanes) { CK(cudaEventRecord(h->lane_join, h->lane_stream)); CK(cudaStreamWaitEvent(st, h->lane_join, 0)); }
+    for (int l = 1; l < nlanes; l++) { CK(cudaEventRecord(h->lane_join[l - 1], h->lane_stream[l - 1])); CK(cudaStreamWaitEvent(st, h->lane_join[l - 1], 0)); }
     return HOGB200_OK;
 }
 

@@ -1,4 +1,2 @@
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for l in 1 0; do echo "HOGB200_LANES=$l (1 = single stream)"; HOGB200_LANES=$l python bench.py --quick --no-cpu --steps 20 --warmup 5 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(round(d['value']), round(d['e2e']['value']), round(d['blocking_call']['value']), round(d['blocking_call']['e2e_value']))"; done
-python tools/race_repeat.py 10 | tail -4
-for w in vga kitti 4k; do HOGB200_LANES=1 python bench.py --workload $w --quick --no-cpu --steps 6 --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('$w single', round(d['value']), round(d['e2e']['value']))"; python bench.py --workload $w --quick --no-cpu --steps 6 --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('$w lanes ', round(d['value']), round(d['e2e']['value']))"; done
+for l in 2 3 4; do for w in 1080p vga kitti 4k dense; do steps=10; [ $w = 4k ] && steps=4; HOGB200_LANES=$l python bench.py --workload $w --quick --no-cpu --steps $steps --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('lanes $l $w', round(d['value']), round(d['e2e']['value']))"; done; done
