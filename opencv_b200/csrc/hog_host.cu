@@ -1141,8 +1141,11 @@ int batch_group(const hogb200* h, int W, int H, int cn)
     enumerate_levels(W, H, h->g.win_w, h->g.win_h, h->scale0, h->nlevels, scales);
     double px = 0;
     for (double s : scales) px += (double)cvRound(W / s) * cvRound(H / s);
-    if ((double)W * H * cn > 16e6) return 2;
-    if (px < 4e6) return px < 1.5e6 ? 16 : 8;
+    // re-measured with two lanes (profiles/r02h_group_lanes.txt): 4K 1 225 / 1 202 / 1 143 fps at 1 / 2 / 4 frames per launch,
+    // 1080p 4 850 / 4 886 / 4 769 at 2 / 4 / 8, KITTI 16 762 / 17 652 at 4 / 8, VGA 33 372 / 33 726 at 8 / 16
+    if ((double)W * H * cn > 16e6) return 1;
+    if (px < 4e6) return 16;
+    if (px < 8e6) return 8;
     return 4;
 }
 
