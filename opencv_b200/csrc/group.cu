@@ -17,6 +17,8 @@
 #include "hog_internal.h"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <algorithm>
 
 namespace hogk {
 
@@ -37,25 +39,49 @@ __global__ void gather_kernel(const RectI* __restrict__ r, const int* __restrict
     if (i < n) { sorted[i] = r[idx[i]]; parent[i] = i; }
 }
 
+// parent[] is read with relaxed GPU-scope loads (L2, where the atomics live): parents only ever decrease, so a value that
+// is stale by the time it is used is harmless
+__device__ __forceinline__ int uf_load(const int* p)
+{
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ int uf_find(int* parent, int a)
 {
-    // parents only ever decrease, so reading a stale one is harmless; halve the path on the way up
-    int p = ((volatile int*)parent)[a];
+    // halve the path on the way up
+    int p = uf_load(parent + a);
     while (p != a) {
-        const int g = ((volatile int*)parent)[p];
+        const int g = uf_load(parent + p);
         if (g != p) atomicMin(&parent[a], g);
         a = p; p = g;
     }
     return a;
 }
 
+// The sweep finds every similar pair, and most of them already sit in one set: the two parents are fetched together and
+// compared before anything else (after path halving most nodes point at their root), and the two climbs to the roots
+// advance in step, so that their loads overlap (the kernel is bound by these dependent L2 round trips: ncu, 55 long-
+// scoreboard stall cycles per issued instruction before this arrangement).
 __device__ __forceinline__ void uf_unite(int* parent, int a, int b)
 {
+    int pa = uf_load(parent + a), pb = uf_load(parent + b);
+    if (pa == pb) return;
     for (;;) {
-        a = uf_find(parent, a); b = uf_find(parent, b);
+        for (;;) {
+            const bool ra = pa == a, rb = pb == b;
+            if (ra && rb) break;
+            const int ga = ra ? pa : uf_load(parent + pa);
+            const int gb = rb ? pb : uf_load(parent + pb);
+            if (!ra) { if (ga != pa) atomicMin(&parent[a], ga); a = pa; pa = ga; }
+            if (!rb) { if (gb != pb) atomicMin(&parent[b], gb); b = pb; pb = gb; }
+        }
         if (a == b) return;
         if (a > b) { const int t = a; a = b; b = t; }
-        if (atomicCAS(&parent[b], b, a) == b) return;      // b was still a root: now under the smaller root a
+        const int old = atomicCAS(&parent[b], b, a);
+        if (old == b) return;                               // b was still a root: now under the smaller root a
+        pa = a; pb = old;                                   // a was a root a moment ago; b has moved under `old`
     }
 }
 
@@ -95,28 +121,20 @@ __global__ void root_flags_kernel(int* __restrict__ parent, int n, int* __restri
         const int r = uf_find(parent, i);
         root_of[i] = r;
         is_root[i] = r == i;
-    }
+    } else if (i == n) is_root[n] = 0;          // the scan runs over n + 1 entries: its last output is the total
 }
 
-// exclusive scan of n ints by ONE CTA of 1024 threads (n is at most a few million and this runs twice per call)
-__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ in, int* __restrict__ out, int n, int* __restrict__ total)
+// exclusive scan of in[0 .. n] (n + 1 entries, in[n] == 0) into out[0 .. n]: out[n] is the total.  (cub::DeviceScan, like the
+// sort a library primitive beside the subject; the single-CTA scan it replaces took 270 us for 100 000 entries.)
+inline size_t scan_bytes(int n)
 {
-    __shared__ int part[1024];
-    const int t = threadIdx.x, per = (n + 1023) / 1024;
-    const int b = min(n, t * per), e = min(n, b + per);
-    int s = 0;
-    for (int i = b; i < e; i++) s += in[i];
-    part[t] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        const int v = t >= d ? part[t - d] : 0;
-        __syncthreads();
-        part[t] += v;
-        __syncthreads();
-    }
-    int off = part[t] - s;
-    for (int i = b; i < e; i++) { const int v = in[i]; out[i] = off; off += v; }
-    if (t == 1023) *total = part[1023];
+    size_t b = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, b, (const int*)nullptr, (int*)nullptr, n + 1);
+    return b;
+}
+inline void exclusive_scan(void* tmp, size_t tmp_bytes, const int* in, int* out, int n, cudaStream_t st)
+{
+    cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in, out, n + 1, st);
 }
 
 // rrects[cls] += rect, rweights[cls]++ (cascadedetect.cpp:86-95); sums = 5 ints per class (x, y, w, h, count)
@@ -144,6 +162,7 @@ __global__ void filter_kernel(const int* __restrict__ sums, int nclasses, int th
                               RectI* __restrict__ mean)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == nclasses) keep[i] = 0;
     if (i >= nclasses) return;
     const int n1 = sums[5 * i + 4];
     const RectI r1 = class_mean(sums + 5 * i);
@@ -176,9 +195,10 @@ size_t group_workspace_bytes(int n)
 {
     size_t sort_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
-    // rects, sorted rects, means, out: 4 x 16 n;  keys x2, idx x2, parent, root_of, flags, scan, keep, pos: 10 x 4 n;
+    sort_bytes = std::max(sort_bytes, scan_bytes(n));
+    // rects, sorted rects, means, out: 4 x 16 n;  keys x2, idx x2, parent, root_of, flags, scan, keep, pos: 10 x 4 (n + 1);
     // sums 20 n; counters
-    return 4 * align256((size_t)16 * n) + 10 * align256((size_t)4 * n) + align256((size_t)20 * n) + align256(sort_bytes) + 512;
+    return 4 * align256((size_t)16 * n) + 10 * align256((size_t)4 * (n + 1)) + align256((size_t)20 * n) + align256(sort_bytes) + 512;
 }
 
 // rects (host, reference order) -> grouped rects (host).  ws: device workspace of group_workspace_bytes(n).
@@ -193,33 +213,33 @@ int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int*
     int* d_keys = (int*)take((size_t)4 * n); int* d_keys2 = (int*)take((size_t)4 * n);
     int* d_idx = (int*)take((size_t)4 * n); int* d_idx2 = (int*)take((size_t)4 * n);
     int* d_parent = (int*)take((size_t)4 * n); int* d_root = (int*)take((size_t)4 * n);
-    int* d_flag = (int*)take((size_t)4 * n); int* d_scan = (int*)take((size_t)4 * n);
-    int* d_keep = (int*)take((size_t)4 * n); int* d_pos = (int*)take((size_t)4 * n);
+    int* d_flag = (int*)take((size_t)4 * (n + 1)); int* d_scan = (int*)take((size_t)4 * (n + 1));
+    int* d_keep = (int*)take((size_t)4 * (n + 1)); int* d_pos = (int*)take((size_t)4 * (n + 1));
     int* d_sums = (int*)take((size_t)20 * n);
-    int* d_cnt = (int*)take(512);
     size_t sort_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
+    sort_bytes = std::max(sort_bytes, scan_bytes(n));
     void* d_sort = take(sort_bytes);
 
-    const int T = 256, B = (n + T - 1) / T;
+    const int T = 256, B = (n + T - 1) / T, B1 = (n + T) / T;
     cudaMemcpyAsync(d_rects, h_rects, (size_t)16 * n, cudaMemcpyHostToDevice, st);
     iota_keys_kernel<<<B, T, 0, st>>>(d_rects, n, d_keys, d_idx);
     cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_keys, d_keys2, d_idx, d_idx2, n, 0, 32, st);
     gather_kernel<<<B, T, 0, st>>>(d_rects, d_idx2, n, d_sorted, d_parent);
     unite_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_idx2, n, eps, d_parent);
-    root_flags_kernel<<<B, T, 0, st>>>(d_parent, n, d_root, d_flag);
-    scan_kernel<<<1, 1024, 0, st>>>(d_flag, d_scan, n, d_cnt);
+    root_flags_kernel<<<B1, T, 0, st>>>(d_parent, n, d_root, d_flag);
+    exclusive_scan(d_sort, sort_bytes, d_flag, d_scan, n, st);
     int nclasses = 0;
-    cudaMemcpyAsync(&nclasses, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&nclasses, d_scan + n, sizeof(int), cudaMemcpyDeviceToHost, st);
     cudaMemsetAsync(d_sums, 0, (size_t)20 * n, st);
     accumulate_kernel<<<B, T, 0, st>>>(d_rects, d_root, d_scan, n, d_sums);
     if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
-    const int BC = (nclasses + T - 1) / T;
+    const int BC = (nclasses + T) / T;            // one thread more than classes: it writes the scan's sentinel
     filter_kernel<<<BC, T, 0, st>>>(d_sums, nclasses, thr, eps, d_keep, d_mean);
-    scan_kernel<<<1, 1024, 0, st>>>(d_keep, d_pos, nclasses, d_cnt + 1);
+    exclusive_scan(d_sort, sort_bytes, d_keep, d_pos, nclasses, st);
     emit_kernel<<<BC, T, 0, st>>>(d_mean, d_keep, d_pos, nclasses, d_out);
     int nout = 0;
-    cudaMemcpyAsync(&nout, d_cnt + 1, sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&nout, d_pos + nclasses, sizeof(int), cudaMemcpyDeviceToHost, st);
     if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
     if (nout > 0) cudaMemcpyAsync(h_out, d_out, (size_t)16 * nout, cudaMemcpyDeviceToHost, st);
     if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) return -1;
@@ -240,13 +260,17 @@ namespace {
 
 struct Cand { int level, x, y; float score; };      // = hogk::Candidate
 
-__global__ void cand_keys_kernel(const Cand* __restrict__ c, int n, int ndet, unsigned long long* __restrict__ keys, int* __restrict__ idx)
+// key = segment | level | y | x, each field as wide as the plan needs (CandGeom bits_*): the radix sort makes one pass per
+// 8 key bits, and 1080p / VGA keys are 26 / 25 bits wide instead of the 52 of a fixed layout
+__global__ void cand_keys_kernel(const Cand* __restrict__ c, int n, int ndet, int bx, int by, int bl,
+                                 unsigned long long* __restrict__ keys, int* __restrict__ idx)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const Cand k = c[i];
     const unsigned seg = (unsigned)(k.level >> 20) * ndet + ((k.level >> 16) & 15);
-    keys[i] = ((unsigned long long)seg << 40) | ((unsigned long long)(k.level & 0xffff) << 28) | ((unsigned long long)k.y << 14) | (unsigned)k.x;
+    keys[i] = ((unsigned long long)seg << (bl + by + bx)) | ((unsigned long long)(k.level & 0xffff) << (by + bx)) |
+              ((unsigned long long)k.y << bx) | (unsigned)k.x;
     idx[i] = i;
 }
 
@@ -262,9 +286,9 @@ __global__ void cand_rects_kernel(const Cand* __restrict__ c, const unsigned lon
     r.x = __double2int_rn((double)(k.x * G.stride_x) * scale); r.y = __double2int_rn((double)(k.y * G.stride_y) * scale);
     r.w = __double2int_rn(G.win_w * scale); r.h = __double2int_rn(G.win_h * scale);
     rects[i] = r;
-    const int sg = (int)(keys[i] >> 40);
+    const int sg = (int)(keys[i] >> (G.bits_x + G.bits_y + G.bits_level));
     seg[i] = sg;
-    xkeys[i] = ((unsigned long long)sg << 32) | (unsigned)r.x;          // r.x >= 0: window origins are inside the level
+    xkeys[i] = ((unsigned long long)sg << G.bits_rx) | (unsigned)r.x;    // 0 <= r.x < 2^bits_rx: window origins are inside the frame
     idx[i] = i;
     if (count_now) atomicAdd(&seg_count[sg], 1);                        // no grouping: every candidate is an output rect
 }
@@ -318,8 +342,8 @@ __global__ void filter_seg_kernel(const int* __restrict__ sums, const int* __res
                                   int* __restrict__ keep, RectI* __restrict__ mean, int* __restrict__ seg_count, int n)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    if (i >= *nclasses_p) { keep[i] = 0; return; }
+    if (i > n) return;
+    if (i >= *nclasses_p) { keep[i] = 0; return; }          // incl. the scan's sentinel keep[n] (nclasses <= n)
     const int n1 = sums[5 * i + 4];
     const RectI r1 = class_mean(sums + 5 * i);
     mean[i] = r1;
@@ -339,10 +363,11 @@ __global__ void filter_seg_kernel(const int* __restrict__ sums, const int* __res
 }
 
 __global__ void emit_seg_kernel(const RectI* __restrict__ mean, const int* __restrict__ keep, const int* __restrict__ pos, int n,
-                                RectI* __restrict__ out)
+                                RectI* __restrict__ out, int* __restrict__ total)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && keep[i]) out[pos[i]] = mean[i];
+    if (i == 0) *total = pos[n];                 // number of output rects of the chunk
 }
 
 __global__ void fill_kernel(int* __restrict__ p, int n, int v)
@@ -363,8 +388,8 @@ size_t sort64_bytes(int n)
 
 size_t cand_group_workspace_bytes(int n, int nseg)
 {
-    return 4 * align256((size_t)16 * n) + 2 * align256((size_t)8 * n) + 12 * align256((size_t)4 * n) + align256((size_t)20 * n) +
-           align256(sort64_bytes(n)) + 4 * align256((size_t)4 * nseg) + 1024;
+    return 4 * align256((size_t)16 * n) + 2 * align256((size_t)8 * n) + 12 * align256((size_t)4 * (n + 1)) + align256((size_t)20 * n) +
+           align256(std::max(sort64_bytes(n), scan_bytes(n))) + 4 * align256((size_t)4 * nseg) + 1024;
 }
 
 // d_cand: n candidates of the chunk in device memory (any order).  On return *d_out_p points at the output rects in the
@@ -381,21 +406,23 @@ int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandG
     int* d_idx = (int*)take((size_t)4 * n); int* d_idx2 = (int*)take((size_t)4 * n);
     int* d_seg = (int*)take((size_t)4 * n); int* d_sseg = (int*)take((size_t)4 * n);
     int* d_parent = (int*)take((size_t)4 * n); int* d_root = (int*)take((size_t)4 * n);
-    int* d_flag = (int*)take((size_t)4 * n); int* d_scan = (int*)take((size_t)4 * n);
-    int* d_keep = (int*)take((size_t)4 * n); int* d_pos = (int*)take((size_t)4 * n);
+    int* d_flag = (int*)take((size_t)4 * (n + 1)); int* d_scan = (int*)take((size_t)4 * (n + 1));
+    int* d_keep = (int*)take((size_t)4 * (n + 1)); int* d_pos = (int*)take((size_t)4 * (n + 1));
     int* d_cseg = (int*)take((size_t)4 * n); int* d_order = (int*)take((size_t)4 * n);
     int* d_sums = (int*)take((size_t)20 * n);
-    size_t sort_bytes = sort64_bytes(n);
+    size_t sort_bytes = std::max(sort64_bytes(n), scan_bytes(n));
     void* d_sort = take(sort_bytes);
     int* d_hdr = (int*)take((size_t)4 * (nseg + 1));       // [total][count per segment]
     int* d_lo = (int*)take((size_t)4 * nseg); int* d_hi = (int*)take((size_t)4 * nseg);
-    int* d_cnt = (int*)take(256);
     const Cand* c = (const Cand*)d_cand;
-    const int T = 256, B = (n + T - 1) / T, BS = (nseg + T - 1) / T;
+    const int T = 256, B = (n + T - 1) / T, B1 = (n + T) / T, BS = (nseg + T - 1) / T;
+    int bseg = 1;
+    while ((1 << bseg) < nseg) bseg++;
+    const int bits1 = bseg + G.bits_level + G.bits_y + G.bits_x, bits2 = bseg + G.bits_rx;
 
     cudaMemsetAsync(d_hdr, 0, (size_t)4 * (nseg + 1), st);
-    cand_keys_kernel<<<B, T, 0, st>>>(c, n, ndet, d_k1, d_idx);
-    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_order, n, 0, 52, st);
+    cand_keys_kernel<<<B, T, 0, st>>>(c, n, ndet, G.bits_x, G.bits_y, G.bits_level, d_k1, d_idx);
+    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_order, n, 0, bits1, st);
     cand_rects_kernel<<<B, T, 0, st>>>(c, d_k2, d_order, n, G, d_rects, d_seg, d_k1, d_idx, d_hdr + 1, thr <= 0);
     *d_hdr_p = d_hdr;
     if (thr <= 0) {             // cv::groupRectangles returns the list untouched (cascadedetect.cpp:66-75)
@@ -403,18 +430,18 @@ int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandG
         *d_out_p = &d_rects[0].x;
         return cudaGetLastError() == cudaSuccess ? 0 : -1;
     }
-    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_idx2, n, 0, 44, st);
+    cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_idx2, n, 0, bits2, st);
     gather_seg_kernel<<<B, T, 0, st>>>(d_rects, d_seg, d_idx2, n, d_sorted, d_sseg, d_parent);
     unite_seg_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_sseg, d_idx2, n, eps, d_parent);
-    root_flags_kernel<<<B, T, 0, st>>>(d_parent, n, d_root, d_flag);
-    scan_kernel<<<1, 1024, 0, st>>>(d_flag, d_scan, n, d_cnt);            // d_cnt[0] = number of classes
+    root_flags_kernel<<<B1, T, 0, st>>>(d_parent, n, d_root, d_flag);
+    exclusive_scan(d_sort, sort_bytes, d_flag, d_scan, n, st);           // d_scan[n] = number of classes
     cudaMemsetAsync(d_sums, 0, (size_t)20 * n, st);
     fill_kernel<<<BS, T, 0, st>>>(d_lo, nseg, 0x7fffffff);
     fill_kernel<<<BS, T, 0, st>>>(d_hi, nseg, -1);
     accumulate_seg_kernel<<<B, T, 0, st>>>(d_rects, d_seg, d_root, d_scan, n, d_sums, d_cseg, d_lo, d_hi);
-    filter_seg_kernel<<<B, T, 0, st>>>(d_sums, d_cnt, d_cseg, d_lo, d_hi, thr, eps, d_keep, d_mean, d_hdr + 1, n);
-    scan_kernel<<<1, 1024, 0, st>>>(d_keep, d_pos, n, d_hdr);              // d_hdr[0] = number of output rects
-    emit_seg_kernel<<<B, T, 0, st>>>(d_mean, d_keep, d_pos, n, d_out);
+    filter_seg_kernel<<<B1, T, 0, st>>>(d_sums, d_scan + n, d_cseg, d_lo, d_hi, thr, eps, d_keep, d_mean, d_hdr + 1, n);
+    exclusive_scan(d_sort, sort_bytes, d_keep, d_pos, n, st);
+    emit_seg_kernel<<<B, T, 0, st>>>(d_mean, d_keep, d_pos, n, d_out, d_hdr);      // d_hdr[0] = number of output rects
     *d_out_p = &d_out[0].x;
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

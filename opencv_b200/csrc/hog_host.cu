@@ -1072,6 +1072,15 @@ CandGeom cand_geom(const hogb200* h, const Plan& P)
     CandGeom G; memset(&G, 0, sizeof G);
     for (size_t i = 0; i < P.lv.size(); i++) G.scale[i] = P.lv[i].scale;
     G.win_w = h->g.win_w; G.win_h = h->g.win_h; G.stride_x = h->win_stride_x; G.stride_y = h->win_stride_y;
+    // widths of the sort-key fields (group.cu): the radix sort makes one pass per 8 key bits
+    auto bits = [](long long v) { int b = 1; while ((1LL << b) <= v) b++; return b; };
+    int mx = 1, my = 1; long long rx = 1;
+    for (const LevelHost& L : P.lv) {
+        mx = std::max(mx, L.nwx); my = std::max(my, L.nwy);
+        rx = std::max(rx, (long long)std::ceil((double)L.nwx * h->win_stride_x * L.scale) + 1);    // > cvRound(x * stride * scale)
+    }
+    G.bits_x = bits(mx); G.bits_y = bits(my); G.bits_level = bits((long long)P.lv.size());
+    G.bits_rx = bits(rx);                          // (from the levels alone: collect() rebuilds the geometry from a job's level list)
     return G;
 }
 

@@ -131,7 +131,10 @@ int group_rectangles_device(const int* h_rects, int n, int thr, double eps, int*
 
 // The tail of detectMultiScale for all (frame, detector) segments of a chunk on the device (group.cu): candidate list ->
 // reference order -> scaled rects -> groupRectangles per segment.  Nothing is synchronised; see group.cu.
-struct CandGeom { double scale[kMaxLevels]; int win_w, win_h, stride_x, stride_y; };
+struct CandGeom {
+    double scale[kMaxLevels]; int win_w, win_h, stride_x, stride_y;
+    int bits_x, bits_y, bits_level, bits_rx;     // key widths: window x / y, level, scaled rect x (radix passes follow the key width)
+};
 size_t cand_group_workspace_bytes(int n, int nseg);
 int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandGeom& G, int thr, double eps, void* ws,
                       cudaStream_t st, const int** d_out_p, const int** d_hdr_p);

@@ -54,6 +54,15 @@ constexpr int kBarBytes = 2 * kMaxRing * 8;  // full[] + empty[] mbarriers at th
 constexpr int kSmemBytes = 227 * 1024;
 constexpr int kMaxChunkC = 8;
 
+#ifdef HOGB200_SVM_TIMING      // experiments only (tools/prof_svm_timing.py): where a consumer warp's cycles go
+__device__ unsigned long long g_svm_timing[160][8][8];
+#define SVM_T(var) const unsigned var = (unsigned)clock64()
+#define SVM_ACC(i, a, b) tacc[i] += (b) - (a)
+#else
+#define SVM_T(var)
+#define SVM_ACC(i, a, b)
+#endif
+
 // how the kernel is laid out for one pass (filled by launch_svm)
 struct SvmPass {
     int nchunks;        // column chunks of C blocks per window row (WBXp = nchunks * C >= win_bx)
@@ -275,10 +284,15 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
     const float* const mycoef = coef + det * S.ncoefp;
     const int crow = wbxp * kHist;                           // floats per coefficient row
     const int q = lane & 7, pr = lane >> 3;
+#ifdef HOGB200_SVM_TIMING
+    unsigned tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};    // dead tiles, first wait, step waits, steps, epilogue, rest wait, live tiles, total
+    const unsigned t_begin = (unsigned)clock64();
+#endif
     for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
         const SvmItem it = items[ii];
         if (it.frame >= fs.nframes) continue;
         const LevelDesc& L = levels[it.level];
+        SVM_T(t_tile);
         const int vwx = L.nbx - win_bx + 1, vwy = L.nby - win_by + 1;   // dense (stride-1) window grid of the level
         const int wx0 = it.wx0 + cg * kT, wy0 = it.wy0 + band * kBandRows;
         // Every warp waits for and releases EVERY row of every tile, in ring order, also the rows (and the whole
@@ -299,6 +313,7 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
                 }
                 __syncwarp();
             }
+            { SVM_T(t_e); SVM_ACC(0, t_tile, t_e); }
             continue;
         }
         if (lane < band * kBandRows + 7) {                          // the rows above the band + the 7 rows steps 0 and 1 read
@@ -307,6 +322,11 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
             if (lane < band * kBandRows) mbar_arrive(empty0 + 8 * (m % ring));
         }
         __syncwarp();
+        SVM_T(t_first);
+        SVM_ACC(1, t_tile, t_first);
+#ifdef HOGB200_SVM_TIMING
+        tacc[6] += 1;
+#endif
 
         float2 accA[kT], accB[kT], exA[2], exB[2];    // (even k, odd k) partial sums of window rows 2pr / 2pr+1
 #pragma unroll
@@ -318,12 +338,15 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
         unsigned npar = ((pos0 + kBandRows - 1) / ring) & 1;
         bool ready = true;
         for (int t = 0; t <= win_by; t++) {
+            SVM_T(t_s0);
             if (!ready) {                                            // the row this step adds: one position before (nslot, npar)
                 const unsigned ps = nslot == 0 ? ring - 1 : nslot - 1, pp = nslot == 0 ? npar ^ 1 : npar;
                 mbar_wait(full0 + 8 * ps, pp);
             }
             // poll the next step's row now, so that the answer is there when this step's arithmetic is done
             ready = t == win_by || mbar_test(full0 + 8 * nslot, npar);
+            SVM_T(t_s1);
+            SVM_ACC(2, t_s0, t_s1);
             const float* rowp = ringp + slot_l * kRowFloats + cg * kT * kHist;
 #ifdef HOGB200_CHECKS       // the row this lane reads is inside the ring, and the producer has declared it full
             if (slot_l >= (unsigned)ring || (cg * kT + kT + wbxp - 1) * kHist > kRowFloats ||
@@ -339,7 +362,9 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
             slot_l = slot_l + 1 == ring ? 0 : slot_l + 1;
             oslot = oslot + 1 == ring ? 0 : oslot + 1;
             if (++nslot == ring) { nslot = 0; npar ^= 1; }
+            { SVM_T(t_s2); SVM_ACC(3, t_s1, t_s2); }
         }
+        SVM_T(t_epi0);
         if (lane < kBandRows - 2) mbar_arrive(empty0 + 8 * ((pos0 + win_by + 1 + lane) % ring));   // the band's last 6 rows
 
         // ---- the 8 lanes of a quarter-warp hold the k-partials of the same 2 x 16 windows: reduce-scatter
@@ -400,13 +425,22 @@ svm_kernel(const __grid_constant__ FrameSet fs, const LevelDesc* __restrict__ le
                 }
             }
         }
+        SVM_T(t_epi1);
+        SVM_ACC(4, t_epi0, t_epi1);
         if (lane < rest) {                                          // rows of the tile below the band
             const unsigned m = pos0 + 7 + win_by + lane;
             mbar_wait(full0 + 8 * (m % ring), (m / ring) & 1);
             mbar_arrive(empty0 + 8 * (m % ring));
         }
         __syncwarp();
+        { SVM_T(t_e); SVM_ACC(5, t_epi1, t_e); }
     }
+#ifdef HOGB200_SVM_TIMING
+    if (lane == 0) {
+        tacc[7] = (unsigned)clock64() - t_begin;
+        for (int i = 0; i < 8; i++) g_svm_timing[blockIdx.x][w][i] += tacc[i];
+    }
+#endif
 }
 
 // One thread block per window: copies the window's WBY x WBX block histograms into the descriptor matrix, in
@@ -543,3 +577,16 @@ void launch_extract(const LevelDesc* d_level0, int nwx, int nwy, const float* d_
 }
 
 }  // namespace hogk
+
+#ifdef HOGB200_SVM_TIMING
+extern "C" int hogb200_debug_svm_timing(unsigned long long* out, int reset)
+{
+    if (out && cudaMemcpyFromSymbol(out, hogk::g_svm_timing, sizeof(unsigned long long) * 160 * 8 * 8) != cudaSuccess) return 1;
+    if (reset) {
+        void* p = nullptr;
+        if (cudaGetSymbolAddress(&p, hogk::g_svm_timing) != cudaSuccess) return 1;
+        if (cudaMemset(p, 0, sizeof(unsigned long long) * 160 * 8 * 8) != cudaSuccess) return 1;
+    }
+    return 0;
+}
+#endif
