@@ -76,6 +76,9 @@ int resize_plan_rows(const ResizeCoef* xt, int dst_w, const ResizeCoef* yt, int 
 // (samples/gpu/tbd.cpp:573-599), moved to the device.  dst rows are 16-byte aligned.
 void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int w, int h, cudaStream_t st);
 // dst = src with a BORDER_REFLECT_101 frame of px / py pixels (cn = 1 or 4; 4-byte aligned rows for cn = 4)
+// rows of up to kMaxGroup flat-uploaded frames (same geometry) to their aligned pitch, 4 bytes per thread
+struct RepitchSet { const uint8_t* src[kMaxGroup]; uint8_t* dst[kMaxGroup]; int n, spitch, dpitch, row_bytes, rows; };
+void launch_repitch(const RepitchSet& rp, cudaStream_t st);
 void launch_pad_reflect101(const uint8_t* src, size_t spitch, int w, int h, int cn, uint8_t* dst, size_t dpitch, int px, int py,
                            cudaStream_t st);
 void launch_resize(const FrameSet& fs, int bw, int bh, int cn,

@@ -551,6 +551,16 @@ bgr_to_bgra_kernel(const uint8_t* __restrict__ src, size_t spitch, uint8_t* __re
     }
 }
 
+// Frames uploaded flat (host rows that are no multiple of 16 bytes, e.g. 1242 x 4): every row to its 64-byte aligned
+// place.  blockIdx.z = frame, one thread = 4 bytes (row_bytes % 4 == 0, both bases 4-byte aligned).
+__global__ void __launch_bounds__(256) repitch_kernel(const __grid_constant__ RepitchSet rp)
+{
+    const int x = 4 * (blockIdx.x * 256 + threadIdx.x), y = blockIdx.y;
+    if (x >= rp.row_bytes) return;
+    const unsigned v = __ldg(reinterpret_cast<const unsigned*>(rp.src[blockIdx.z] + (size_t)y * rp.spitch + x));
+    *reinterpret_cast<unsigned*>(rp.dst[blockIdx.z] + (size_t)y * rp.dpitch + x) = v;
+}
+
 // Image + border, BORDER_REFLECT_101 (cv::borderInterpolate, core/src/copy.cpp): dst(y, x) = src(r(y - py), r(x - px)).
 // One thread per destination pixel (BPP = bytes per pixel, 1 or 4).  Feeds the ROI path, whose windows may reach into
 // the padding the CPU class puts around an image (objdetect/src/hog.cpp:3566-3570).
@@ -578,6 +588,12 @@ void launch_bgr_to_bgra(const uint8_t* src, size_t spitch, uint8_t* dst, size_t 
     if (w <= 0 || h <= 0) return;
     const int aligned = ((uintptr_t)src % 4 == 0) && (spitch % 4 == 0);
     bgr_to_bgra_kernel<<<dim3((w + 255) / 256, (h + 3) / 4), 256, 0, st>>>(src, spitch, dst, dpitch, w, h, aligned);
+}
+
+void launch_repitch(const RepitchSet& rp, cudaStream_t st)
+{
+    if (rp.n <= 0 || rp.rows <= 0 || rp.row_bytes <= 0) return;
+    repitch_kernel<<<dim3((rp.row_bytes / 4 + 255) / 256, rp.rows, rp.n), 256, 0, st>>>(rp);
 }
 
 void launch_pad_reflect101(const uint8_t* src, size_t spitch, int w, int h, int cn, uint8_t* dst, size_t dpitch, int px, int py,
