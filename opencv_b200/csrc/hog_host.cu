@@ -504,6 +504,12 @@ int stage_frame(hogb200* h, const hogb200_image* img, int buf, cudaStream_t st, 
     }
     const size_t pitch = align_up(row, 64);
     CK(h->d_frame[buf].reserve(pitch * img->height + 64));
+    if (allow_raw && img->on_device && row % 4 == 0 && img->pitch % 4 == 0 && (uintptr_t)img->data % 4 == 0 && flat_upload()) {
+        // a device frame whose rows are not 16-byte aligned: the re-pitch kernel reads it where it lies
+        out.dev = h->d_frame[buf].p; out.pitch = (int)pitch;
+        out.raw = (const uint8_t*)img->data; out.raw_pitch = (int)img->pitch; out.row_bytes = (int)row; out.rows = img->height;
+        return HOGB200_OK;
+    }
     if (allow_raw && !img->on_device && img->pitch == row && pitch != row && row % 4 == 0 && flat_upload()) {
         // a contiguous host frame whose rows are not 64-byte multiples (1242 x 4 = 4968 bytes): a 2-D host->device copy of
         // such rows reaches 31 GB/s, a flat one 54 GB/s; the rows are moved to their aligned places by a kernel on the
