@@ -9,7 +9,8 @@
 //   * classes = connected components of SimilarRects; cv::partition numbers them by first appearance, i.e. by the
 //     smallest member index.  Here: lock-free union-find whose hooking always puts the larger root under the
 //     smaller one, so a root IS the smallest member; an exclusive scan over the root flags gives the class number.
-//   * candidate pairs: rects sorted by x (CUB radix sort, the one library call -- a sort is not the subject here);
+//   * candidate pairs: rects sorted by x (CUB radix sort; with the CUB prefix scan below the two library primitives of this file -- a
+//     sort and a scan are not the subject here -- both outside the three pipeline kernels);
 //     a warp owns one rect and sweeps the sorted order to the right while x_b - x_a <= eps (w_a + h_a) / 2, which
 //     bounds SimilarRects' own delta from above (the host's sweep, hog_host.cu group_rectangles).
 //   * class sums in int32 atomics (order-free, exact), mean with float s = 1.f / n and round-half-even, the
