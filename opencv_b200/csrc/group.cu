@@ -170,16 +170,30 @@ inline void exclusive_scan(void* tmp, size_t tmp_bytes, const int* in, int* out,
     cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in, out, n + 1, st);
 }
 
+// sums[cls] += (x, y, w, h, 1) for the rect of every lane: the lanes of a warp that hold the same class (neighbours in
+// reference order mostly do -- with a few big classes, 100 000 rects otherwise queue up on a handful of addresses) add up
+// among themselves first and their first lane issues the five atomics.  Integer sums: exact in any order.
+__device__ __forceinline__ void class_add(int* __restrict__ sums, int cls, const RectI& r, bool live)
+{
+    const unsigned act = __ballot_sync(0xffffffffu, live);
+    if (!live) return;
+    const unsigned peers = __match_any_sync(act, cls);
+    const int x = __reduce_add_sync(peers, r.x), y = __reduce_add_sync(peers, r.y), w = __reduce_add_sync(peers, r.w),
+              h = __reduce_add_sync(peers, r.h);
+    if ((threadIdx.x & 31) == __ffs(peers) - 1) {
+        int* s = sums + 5 * cls;
+        atomicAdd(s + 0, x); atomicAdd(s + 1, y); atomicAdd(s + 2, w); atomicAdd(s + 3, h);
+        atomicAdd(s + 4, __popc(peers));
+    }
+}
+
 // rrects[cls] += rect, rweights[cls]++ (cascadedetect.cpp:86-95); sums = 5 ints per class (x, y, w, h, count)
 __global__ void accumulate_kernel(const RectI* __restrict__ r, const int* __restrict__ root_of, const int* __restrict__ class_of_root,
                                   int n, int* __restrict__ sums)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        int* s = sums + 5 * class_of_root[root_of[i]];
-        atomicAdd(s + 0, r[i].x); atomicAdd(s + 1, r[i].y); atomicAdd(s + 2, r[i].w); atomicAdd(s + 3, r[i].h);
-        atomicAdd(s + 4, 1);
-    }
+    const bool live = i < n;
+    class_add(sums, live ? class_of_root[root_of[i]] : 0, live ? r[i] : RectI{0, 0, 0, 0}, live);
 }
 
 // mean rect of a class: Rect(saturate_cast<int>(r.x * s), ...) with float s = 1.f / n (cascadedetect.cpp:97-106)
@@ -345,11 +359,10 @@ __global__ void accumulate_seg_kernel(const RectI* __restrict__ r, const int* __
                                       int* __restrict__ seg_lo, int* __restrict__ seg_hi)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int cls = class_of_root[root_of[i]];
-    int* s = sums + 5 * cls;
-    atomicAdd(s + 0, r[i].x); atomicAdd(s + 1, r[i].y); atomicAdd(s + 2, r[i].w); atomicAdd(s + 3, r[i].h);
-    atomicAdd(s + 4, 1);
+    const bool live = i < n;
+    const int cls = live ? class_of_root[root_of[i]] : 0;
+    class_add(sums, cls, live ? r[i] : RectI{0, 0, 0, 0}, live);
+    if (!live) return;
     if (root_of[i] == i) {
         class_seg[cls] = seg[i];
         atomicMin(&seg_lo[seg[i]], cls); atomicMax(&seg_hi[seg[i]], cls);

@@ -1,2 +1,5 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for l in 2 3 4; do for w in 1080p vga kitti 4k dense; do steps=10; [ $w = 4k ] && steps=4; HOGB200_LANES=$l python bench.py --workload $w --quick --no-cpu --steps $steps --warmup 3 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('lanes $l $w', round(d['value']), round(d['e2e']['value']))"; done; done
+mkdir -p gpurun_out
+python -m pytest tests -x -q -m gpu -k "tail or group or dense or submit or hits or edge" 2>&1 | tail -3
+python tools/prof_tail.py 640 480 1 256 4 | tail -1
+python tools/prof_group.py 2>&1 | tail -4
+ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/prof_tail_vga_launches6.csv python tools/prof_tail.py 640 480 1 256 1 > gpurun_out/prof_tail_ncu.log 2>&1
