@@ -396,6 +396,30 @@ def test_bgr_input_equals_bgra(hog, port, shape):
     hog.setHitThreshold(0.0)
 
 
+@pytest.mark.parametrize("shape", [(1242, 375, 4), (644, 480, 1), (333, 251, 4), (642, 300, 1)])
+def test_batch_frames_with_unaligned_rows(hog, shape):
+    """Batch path, frames whose rows are no multiple of 16 bytes: contiguous host frames go up as one flat copy and are
+    re-pitched by a kernel on the compute stream, device frames are re-pitched where they lie (hog_host.cu stage_frame;
+    rows that are no multiple of 4 bytes keep the 2-D copy): always the single-frame path's result, which stages through
+    a 2-D copy; submit / collect included."""
+    import torch
+    w, h, cn = shape
+    frames = [synthetic_frame(6100 + 7 * i + w, w, h, cn, silhouettes=3) for i in range(5)]
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+    hog.setHitThreshold(-1.5); hog.setGroupThreshold(0)
+    try:
+        want = [hog.detectMultiScale(f) for f in frames]
+        assert sum(len(x) for x in want) > 0
+        for src in (frames, dev, [frames[0], dev[1], frames[2], dev[3], frames[4]]):
+            got = hog.detectMultiScaleBatch(src)
+            assert all(np.array_equal(a, b) for a, b in zip(got, want))
+        t = hog.submitBatch(frames)
+        got = hog.collectBatch(t)
+        assert all(np.array_equal(a, b) for a, b in zip(got, want))
+    finally:
+        hog.setHitThreshold(0.0); hog.setGroupThreshold(2)
+
+
 def test_save_load_detector_file(hog, tmp_path):
     """cv::cuda::HOG::save / load (cudaobjdetect/src/hog.cpp:599-679) with the detector included: a handle created from
     the file detects exactly what the original does; the reference's own writer output loads as well."""
