@@ -101,6 +101,7 @@ __device__ __forceinline__ bool similar(const RectI& r1, const RectI& r2, double
 // rects, ~8 partners per rect) uniting on the spot is 9 % faster (460 against 501 us per 105 000 rects), so each kernel
 // takes its own form.  (A THREAD per rect with batched unites was measured too: 828 us.)
 constexpr int kUniteWarps = 8, kHits = 224;
+constexpr int kSegCap = 8192, kSegThreads = 1024, kTabMax = 4096;       // unite_seg_smem_kernel: rects per segment it takes (24 B of shared memory each), threads per CTA
 
 template <bool SEG, bool COLLECT>
 __device__ __forceinline__ void unite_sweep(const RectI* __restrict__ sorted, const int* __restrict__ sorted_seg,
@@ -347,10 +348,95 @@ __global__ void gather_seg_kernel(const RectI* __restrict__ r, const int* __rest
     if (i < n) { sorted[i] = r[idx[i]]; sorted_seg[i] = seg[idx[i]]; parent[i] = i; }
 }
 
+// (segments of at most kSegCap rects have been grouped in shared memory by unite_seg_smem_kernel)
 __global__ void __launch_bounds__(kUniteWarps * 32) unite_seg_kernel(const RectI* __restrict__ sorted, const int* __restrict__ sorted_seg,
-                                                                     const int* __restrict__ idx, int n, double eps, int* __restrict__ parent)
+                                                                     const int* __restrict__ idx, int n, double eps, int* __restrict__ parent,
+                                                                     const int* __restrict__ s0, const int* __restrict__ s1, int done_below)
 {
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= n) return;
+    const int sg = sorted_seg[a];
+    if (s1[sg] - s0[sg] <= done_below) return;
     unite_sweep<true, false>(sorted, sorted_seg, idx, n, eps, parent, nullptr);
+}
+
+// [s0[s], s1[s]) = the rects of segment s (the same range in reference order and in x order: both sorts are segment-major)
+__global__ void seg_bounds_kernel(const int* __restrict__ seg, int n, int* __restrict__ s0, int* __restrict__ s1)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int s = seg[i];
+    if (i == 0 || seg[i - 1] != s) s0[s] = i;
+    if (i == n - 1 || seg[i + 1] != s) s1[s] = i + 1;
+}
+
+// union-find on a parent array in SHARED memory (indices local to a segment); same hooking rule as uf_unite
+__device__ __forceinline__ int ufs_find(int* parent, int a)
+{
+    int p = ((volatile int*)parent)[a];
+    while (p != a) {
+        const int g = ((volatile int*)parent)[p];
+        if (g != p) atomicMin(&parent[a], g);
+        a = p; p = g;
+    }
+    return a;
+}
+__device__ __forceinline__ void ufs_unite(int* parent, int a, int b)
+{
+    if (((volatile int*)parent)[a] == ((volatile int*)parent)[b]) return;
+    for (;;) {
+        a = ufs_find(parent, a); b = ufs_find(parent, b);
+        if (a == b) return;
+        if (a > b) { const int t = a; a = b; b = t; }
+        if (atomicCAS(&parent[b], b, a) == b) return;
+    }
+}
+
+// One CTA per segment of at most kSegCap rects: the segment's rects and its union-find live in shared memory (a rect or a
+// parent costs ~30 cycles instead of an L2 round trip -- the sweep is a chain of such dependent reads), warps take the
+// segment's rects in turn and sweep as unite_sweep does; at the end every rect's ROOT goes to the global parent array.
+// Larger segments are left to unite_seg_kernel.
+
+__global__ void __launch_bounds__(kSegThreads) unite_seg_smem_kernel(const RectI* __restrict__ sorted, const int* __restrict__ idx,
+                                                                     const int* __restrict__ s0, const int* __restrict__ s1,
+                                                                     double eps, int mmax, int* __restrict__ parent)
+{
+    extern __shared__ __align__(16) unsigned char seg_smem[];
+    const int r0 = s0[blockIdx.x], r1 = s1[blockIdx.x], ns = r1 - r0;
+    if (ns <= 1 || ns > kSegCap) return;
+    // the segment's rects (x order), their reference positions and the union-find parents, all local to the segment
+    RectI* srect = reinterpret_cast<RectI*>(seg_smem);
+    int* sidx = reinterpret_cast<int*>(seg_smem + (size_t)16 * kSegCap);
+    int* lparent = sidx + kSegCap;
+    int* dtab = lparent + kSegCap;
+    for (int i = threadIdx.x; i < ns; i += kSegThreads) { srect[i] = sorted[r0 + i]; sidx[i] = idx[r0 + i] - r0; lparent[i] = i; }
+    // SimilarRects compares integer differences with delta = eps * (min w + min h) * 0.5 in double: |d| <= delta is
+    // |d| <= floor(delta), so the doubles are spent once per possible sum m (the same expression, the same rounding)
+    // and the sweep is integer arithmetic -- the FP64 chain was what an iteration waited for once the loads were local
+    for (int m = threadIdx.x; m <= mmax; m += kSegThreads) dtab[m] = __double2int_rd(eps * m * 0.5);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    for (int a = threadIdx.x >> 5; a < ns; a += kSegThreads / 32) {
+        const RectI ra = srect[a];
+        const int ia = sidx[a];
+        const int reach = dtab[ra.w + ra.h];
+        for (int b = a + 1 + lane; ; b += 32) {
+            bool in_reach = false;
+            if (b < ns) {
+                const RectI rb = srect[b];
+                in_reach = rb.x - ra.x <= reach;
+                if (in_reach) {
+                    const int delta = dtab[min(ra.w, rb.w) + min(ra.h, rb.h)];
+                    if (abs(ra.x - rb.x) <= delta && abs(ra.y - rb.y) <= delta && abs(ra.x + ra.w - rb.x - rb.w) <= delta &&
+                        abs(ra.y + ra.h - rb.y - rb.h) <= delta)
+                        ufs_unite(lparent, ia, sidx[b]);
+                }
+            }
+            if (!__any_sync(0xffffffffu, in_reach)) break;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ns; i += kSegThreads) parent[r0 + i] = r0 + ufs_find(lparent, i);
 }
 
 // sums = 5 ints per class; class -> segment, and every segment's class range [seg_lo, seg_hi]
@@ -421,7 +507,7 @@ size_t sort64_bytes(int n)
 size_t cand_group_workspace_bytes(int n, int nseg)
 {
     return 4 * align256((size_t)16 * n) + 2 * align256((size_t)8 * n) + 12 * align256((size_t)4 * (n + 1)) + align256((size_t)20 * n) +
-           align256(std::max(sort64_bytes(n), scan_bytes(n))) + 4 * align256((size_t)4 * nseg) + 1024;
+           align256(std::max(sort64_bytes(n), scan_bytes(n))) + 6 * align256((size_t)4 * (nseg + 1)) + 1024;
 }
 
 // d_cand: n candidates of the chunk in device memory (any order).  On return *d_out_p points at the output rects in the
@@ -446,6 +532,7 @@ int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandG
     void* d_sort = take(sort_bytes);
     int* d_hdr = (int*)take((size_t)4 * (nseg + 1));       // [total][count per segment]
     int* d_lo = (int*)take((size_t)4 * nseg); int* d_hi = (int*)take((size_t)4 * nseg);
+    int* d_s0 = (int*)take((size_t)4 * nseg); int* d_s1 = (int*)take((size_t)4 * nseg);
     const Cand* c = (const Cand*)d_cand;
     const int T = 256, B = (n + T - 1) / T, B1 = (n + T) / T, BS = (nseg + T - 1) / T;
     int bseg = 1;
@@ -464,7 +551,25 @@ int cand_group_device(const void* d_cand, int n, int nseg, int ndet, const CandG
     }
     cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_k1, d_k2, d_idx, d_idx2, n, 0, bits2, st);
     gather_seg_kernel<<<B, T, 0, st>>>(d_rects, d_seg, d_idx2, n, d_sorted, d_sseg, d_parent);
-    unite_seg_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_sseg, d_idx2, n, eps, d_parent);
+    cudaMemsetAsync(d_s0, 0, (size_t)4 * nseg, st);
+    cudaMemsetAsync(d_s1, 0, (size_t)4 * nseg, st);
+    seg_bounds_kernel<<<B, T, 0, st>>>(d_seg, n, d_s0, d_s1);
+    // the largest w + h a rect of this plan can have (cvRound(win * scale) of the last level): the size of the delta table
+    double smax = 1.0;
+    for (int l = 0; l < kMaxLevels; l++) smax = std::max(smax, G.scale[l]);
+    const int mmax = (int)std::ceil(G.win_w * smax) + (int)std::ceil(G.win_h * smax) + 2;
+    const bool in_smem = mmax < kTabMax;
+    if (in_smem) {
+        constexpr int smem = kSegCap * 24 + kTabMax * 4;
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (!attr_set[dev & 63])
+            attr_set[dev & 63] = cudaFuncSetAttribute(unite_seg_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess;
+        unite_seg_smem_kernel<<<nseg, kSegThreads, smem, st>>>(d_sorted, d_idx2, d_s0, d_s1, eps, mmax, d_parent);
+    }
+    unite_seg_kernel<<<(int)(((long long)n * 32 + T - 1) / T), T, 0, st>>>(d_sorted, d_sseg, d_idx2, n, eps, d_parent, d_s0, d_s1,
+                                                                           in_smem ? kSegCap : 0);
     root_flags_kernel<<<B1, T, 0, st>>>(d_parent, n, d_root, d_flag);
     exclusive_scan(d_sort, sort_bytes, d_flag, d_scan, n, st);           // d_scan[n] = number of classes
     cudaMemsetAsync(d_sums, 0, (size_t)20 * n, st);
